@@ -1,0 +1,356 @@
+// p2p.cu -- probe (b): all-pairs NVLink copy + checksum.  New capability: the reference never
+// touches a second GPU (its only kernel runs on device 0; SURVEY.md section 2 kernel inventory).
+//
+// For a directed pair src -> dst the kernel runs on dst and LOADS src's buffer through the
+// peer mapping (the loads are the NVLink traffic: requests travel dst -> src, data returns
+// src -> dst through NVSwitch), stores the words into a local buffer and reduces
+// sum(uint32) -> uint64 and xor with warp shuffles.  The copy and the checksum are one pass:
+// 1 x bytes over NVLink, 1 x bytes of local HBM writes, nothing re-read.
+//
+// Remote latency is microseconds, so every thread keeps UNROLL 128-bit loads in flight and
+// the grid is persistent (k CTAs per SM) to put tens of MB in flight chip-wide.
+#include <future>
+
+#include "common.cuh"
+#include "gen.cuh"
+
+namespace gp {
+
+constexpr int P2P_THREADS = 512;
+constexpr int P2P_UNROLL = 8;
+constexpr int P2P_MAX_BLOCKS = 148 * 4;
+
+struct P2PScratch {
+    uint64_t out_sum;
+    uint32_t out_xor;
+    unsigned int ticket;  // 0 at launch; the last CTA resets it
+    uint64_t partial_sum[P2P_MAX_BLOCKS];
+    uint32_t partial_xor[P2P_MAX_BLOCKS];
+};
+
+__global__ void __launch_bounds__(P2P_THREADS)
+p2p_copy_checksum_kernel(const uint4 *__restrict__ src_peer, uint4 *__restrict__ dst_local, uint64_t n16,
+                         P2PScratch *scr) {
+    uint64_t s = 0;
+    uint32_t x = 0;
+    constexpr uint64_t TILE = static_cast<uint64_t>(P2P_THREADS) * P2P_UNROLL;
+    const uint64_t n_tiles = n16 / TILE;
+    for (uint64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const uint64_t base = t * TILE + threadIdx.x;
+        uint4 v[P2P_UNROLL];
+#pragma unroll
+        for (int u = 0; u < P2P_UNROLL; ++u) v[u] = ldg128_stream(src_peer + base + u * P2P_THREADS);
+#pragma unroll
+        for (int u = 0; u < P2P_UNROLL; ++u) {
+            stg128_stream(dst_local + base + u * P2P_THREADS, v[u]);
+            s += static_cast<uint64_t>(v[u].x) + v[u].y + static_cast<uint64_t>(v[u].z) + v[u].w;
+            x ^= v[u].x ^ v[u].y ^ v[u].z ^ v[u].w;
+        }
+    }
+    // ragged remainder (< one tile), grid-strided one vector at a time
+    for (uint64_t i = n_tiles * TILE + static_cast<uint64_t>(blockIdx.x) * P2P_THREADS + threadIdx.x; i < n16;
+         i += static_cast<uint64_t>(gridDim.x) * P2P_THREADS) {
+        const uint4 v = ldg128_stream(src_peer + i);
+        stg128_stream(dst_local + i, v);
+        s += static_cast<uint64_t>(v.x) + v.y + static_cast<uint64_t>(v.z) + v.w;
+        x ^= v.x ^ v.y ^ v.z ^ v.w;
+    }
+
+    __shared__ uint64_t sh_s[P2P_THREADS / 32];
+    __shared__ uint32_t sh_x[P2P_THREADS / 32];
+    __shared__ bool is_last;
+    s = warp_sum_u64(s);
+    x = warp_xor_u32(x);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) {
+        sh_s[warp] = s;
+        sh_x[warp] = x;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint64_t bs = 0;
+        uint32_t bx = 0;
+        for (int i = 0; i < P2P_THREADS / 32; ++i) {
+            bs += sh_s[i];
+            bx ^= sh_x[i];
+        }
+        scr->partial_sum[blockIdx.x] = bs;
+        scr->partial_xor[blockIdx.x] = bx;
+        __threadfence();
+        is_last = (atomicAdd(&scr->ticket, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        uint64_t ts = 0;
+        uint32_t tx = 0;
+        for (unsigned int i = threadIdx.x; i < gridDim.x; i += blockDim.x) {
+            ts += *(volatile uint64_t *)(scr->partial_sum + i);
+            tx ^= *(volatile uint32_t *)(scr->partial_xor + i);
+        }
+        ts = warp_sum_u64(ts);
+        tx = warp_xor_u32(tx);
+        __syncthreads();
+        if (lane == 0) {
+            sh_s[warp] = ts;
+            sh_x[warp] = tx;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint64_t bs = 0;
+            uint32_t bx = 0;
+            for (int i = 0; i < P2P_THREADS / 32; ++i) {
+                bs += sh_s[i];
+                bx ^= sh_x[i];
+            }
+            scr->out_sum = bs;
+            scr->out_xor = bx;
+            scr->ticket = 0;
+        }
+    }
+}
+
+struct P2PDev {
+    int ord = -1;
+    DeviceState *st = nullptr;
+    uint32_t *src = nullptr;  // this device's source words (read by its peers)
+    uint32_t *dst = nullptr;  // landing buffer for the copy this device performs
+    P2PScratch *scr = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    uint64_t exp_sum = 0;
+    uint32_t exp_xor = 0;
+};
+
+static int p2p_grid(const DeviceState &st, uint64_t n16) {
+    const uint64_t tiles = n16 / (static_cast<uint64_t>(P2P_THREADS) * P2P_UNROLL) + 1;
+    const uint64_t cap = std::min<uint64_t>(static_cast<uint64_t>(st.sm_count) * 4, P2P_MAX_BLOCKS);
+    return static_cast<int>(std::max<uint64_t>(1, std::min(tiles, cap)));
+}
+
+}  // namespace gp
+
+using namespace gp;
+
+extern "C" int gpuprobe_p2p_matrix(const gpuprobe_p2p_cfg *cfg, gpuprobe_p2p_cell *cells, char *err, size_t errlen) {
+    if (!cfg || !cells) {
+        set_err(err, errlen, "null cfg/cells");
+        return GPUPROBE_EINVAL;
+    }
+    const int nd = cfg->ndev;
+    if (nd < 2 || nd > MAX_DEVICES || cfg->iters < 1 || cfg->warmup < 0 || cfg->bytes_per_pair == 0 ||
+        (cfg->bytes_per_pair & 15u) || (cfg->mode != GPUPROBE_P2P_SERIAL && cfg->mode != GPUPROBE_P2P_ROUNDS)) {
+        set_err(err, errlen, "bad p2p cfg: ndev=%d bytes=%llu iters=%d warmup=%d mode=%d", nd,
+                (unsigned long long)cfg->bytes_per_pair, cfg->iters, cfg->warmup, cfg->mode);
+        return GPUPROBE_EINVAL;
+    }
+    std::memset(cells, 0, sizeof(gpuprobe_p2p_cell) * nd * nd);
+    const uint64_t bytes = cfg->bytes_per_pair, nwords = bytes / 4, n16 = bytes / 16;
+    const double peak = cfg->peak_gbps > 0 ? cfg->peak_gbps : 900.0;
+
+    std::vector<P2PDev> D(nd);
+    for (int i = 0; i < nd; ++i) {
+        D[i].ord = cfg->devs ? cfg->devs[i] : i;
+        for (int j = 0; j < i; ++j)
+            if (D[j].ord == D[i].ord) {
+                set_err(err, errlen, "device %d listed twice", D[i].ord);
+                return GPUPROBE_EINVAL;
+            }
+        int rc = use_device(D[i].ord, &D[i].st, err, errlen);
+        if (rc) return rc;
+    }
+    // serialise against other probes on these devices; lock in ordinal order
+    std::vector<int> order(nd);
+    for (int i = 0; i < nd; ++i) order[i] = i;
+    std::sort(order.begin(), order.end(), [&](int x, int y) { return D[x].ord < D[y].ord; });
+    std::vector<std::unique_lock<std::mutex>> locks;
+    for (int i : order) locks.emplace_back(D[i].st->mu);
+
+    // expected checksums on the host, overlapped with the GPU work
+    std::vector<std::future<void>> expect;
+    const int host_thr = std::max(1u, std::thread::hardware_concurrency() / static_cast<unsigned>(nd));
+    for (int i = 0; i < nd; ++i)
+        expect.emplace_back(std::async(std::launch::async, [&, i]() {
+            gpuprobe_p2p_expected(nwords, cfg->seed, D[i].ord, host_thr, &D[i].exp_sum, &D[i].exp_xor);
+        }));
+
+    int rc = GPUPROBE_OK;
+    auto cleanup = [&]() {
+        for (auto &f : expect)
+            if (f.valid()) f.wait();
+        for (auto &d : D) {
+            if (cudaSetDevice(d.ord) != cudaSuccess) continue;
+            cudaDeviceSynchronize();
+            cudaFree(d.src);
+            cudaFree(d.dst);
+            cudaFree(d.scr);
+            if (d.ev0) cudaEventDestroy(d.ev0);
+            if (d.ev1) cudaEventDestroy(d.ev1);
+        }
+        (void)cudaGetLastError();
+    };
+#define GP_TRY(call)                                                                                   \
+    do {                                                                                               \
+        cudaError_t e_ = (call);                                                                       \
+        if (e_ != cudaSuccess) {                                                                       \
+            set_err(err, errlen, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            (void)cudaGetLastError();                                                                  \
+            cleanup();                                                                                 \
+            return e_ == cudaErrorMemoryAllocation ? GPUPROBE_ENOMEM : GPUPROBE_ECUDA;                 \
+        }                                                                                              \
+    } while (0)
+
+    // buffers, source words, peer mappings
+    for (auto &d : D) {
+        GP_TRY(cudaSetDevice(d.ord));
+        GP_TRY(cudaMalloc(&d.src, bytes));
+        GP_TRY(cudaMalloc(&d.dst, bytes));
+        GP_TRY(cudaMalloc(&d.scr, sizeof(P2PScratch)));
+        GP_TRY(cudaMemsetAsync(d.scr, 0, sizeof(P2PScratch), d.st->stream));
+        GP_TRY(cudaEventCreate(&d.ev0));
+        GP_TRY(cudaEventCreate(&d.ev1));
+        rc = launch_fill_words(*d.st, d.src, nwords, hash_base(cfg->seed, stream_p2p(d.ord)), d.st->stream, err, errlen);
+        if (rc) {
+            cleanup();
+            return rc;
+        }
+    }
+    bool missing_peer = false;
+    for (int s = 0; s < nd; ++s)
+        for (int t = 0; t < nd; ++t) {
+            gpuprobe_p2p_cell &c = cells[s * nd + t];
+            c.src = D[s].ord;
+            c.dst = D[t].ord;
+            if (s == t) continue;
+            int can = 0;
+            GP_TRY(cudaDeviceCanAccessPeer(&can, D[t].ord, D[s].ord));
+            c.peer_ok = can;
+            if (!can) {
+                missing_peer = true;
+                continue;
+            }
+            GP_TRY(cudaSetDevice(D[t].ord));
+            cudaError_t e = cudaDeviceEnablePeerAccess(D[s].ord, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) {
+                (void)cudaGetLastError();
+            } else {
+                GP_TRY(e);
+            }
+        }
+    for (auto &d : D) {
+        GP_TRY(cudaSetDevice(d.ord));
+        GP_TRY(cudaStreamSynchronize(d.st->stream));
+    }
+
+    // One timed launch of src -> dst on dst's stream (events recorded around it).
+    auto launch_pair = [&](int s, int t, bool timed) -> cudaError_t {
+        P2PDev &dd = D[t];
+        cudaError_t e = cudaSetDevice(dd.ord);
+        if (e != cudaSuccess) return e;
+        if (timed && (e = cudaEventRecord(dd.ev0, dd.st->stream)) != cudaSuccess) return e;
+        p2p_copy_checksum_kernel<<<p2p_grid(*dd.st, n16), P2P_THREADS, 0, dd.st->stream>>>(
+            reinterpret_cast<const uint4 *>(D[s].src), reinterpret_cast<uint4 *>(dd.dst), n16, dd.scr);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        if (timed) e = cudaEventRecord(dd.ev1, dd.st->stream);
+        return e;
+    };
+    // After the pair's launches: read the kernel's checksum, digest the landed copy, fill the cell.
+    auto finish_pair = [&](int s, int t, std::vector<float> &ms) -> int {
+        P2PDev &dd = D[t];
+        gpuprobe_p2p_cell &c = cells[s * nd + t];
+        P2PScratch head{};
+        GP_CUDA(cudaSetDevice(dd.ord));
+        GP_CUDA(cudaMemcpyAsync(&head, dd.scr, 16, cudaMemcpyDeviceToHost, dd.st->stream));
+        GP_CUDA(cudaStreamSynchronize(dd.st->stream));
+        uint64_t land_sum = 0;
+        uint32_t land_xor = 0;
+        int r = run_digest(*dd.st, dd.dst, nwords, &land_sum, &land_xor, dd.st->stream, err, errlen);
+        if (r) return r;
+        expect[s].wait();
+        c.checksum_expected = D[s].exp_sum;
+        c.xor_expected = D[s].exp_xor;
+        c.checksum_got = head.out_sum;
+        c.xor_got = head.out_xor;
+        c.verified = (head.out_sum == D[s].exp_sum && head.out_xor == D[s].exp_xor && land_sum == D[s].exp_sum &&
+                      land_xor == D[s].exp_xor)
+                         ? 1
+                         : 0;
+        c.ms_best = *std::min_element(ms.begin(), ms.end());
+        c.ms_median = median_of(ms);
+        c.gbps = c.ms_median > 0 ? bytes / (c.ms_median * 1e6) : 0;
+        c.frac_of_peak = c.gbps / peak;
+        return GPUPROBE_OK;
+    };
+
+    if (cfg->mode == GPUPROBE_P2P_SERIAL) {
+        for (int s = 0; s < nd && rc == GPUPROBE_OK; ++s)
+            for (int t = 0; t < nd; ++t) {
+                if (s == t || !cells[s * nd + t].peer_ok) continue;
+                P2PDev &dd = D[t];
+                GP_TRY(cudaSetDevice(dd.ord));
+                GP_TRY(cudaMemsetAsync(dd.dst, 0, bytes, dd.st->stream));
+                for (int i = 0; i < cfg->warmup; ++i) GP_TRY(launch_pair(s, t, false));
+                std::vector<float> ms(cfg->iters);
+                for (int i = 0; i < cfg->iters; ++i) {
+                    GP_TRY(launch_pair(s, t, true));
+                    GP_TRY(cudaEventSynchronize(dd.ev1));
+                    GP_TRY(cudaEventElapsedTime(&ms[i], dd.ev0, dd.ev1));
+                }
+                rc = finish_pair(s, t, ms);
+                if (rc) break;
+            }
+    } else {
+        for (int r = 1; r < nd && rc == GPUPROBE_OK; ++r) {
+            // round r: every device reads from the peer r places behind it -> each GPU sends and receives at once
+            std::vector<std::vector<float>> ms(nd);
+            for (int s = 0; s < nd; ++s) {
+                const int t = (s + r) % nd;
+                if (!cells[s * nd + t].peer_ok) continue;
+                GP_TRY(cudaSetDevice(D[t].ord));
+                GP_TRY(cudaMemsetAsync(D[t].dst, 0, bytes, D[t].st->stream));
+            }
+            for (int i = 0; i < cfg->warmup + cfg->iters; ++i) {
+                const bool timed = i >= cfg->warmup;
+                for (int s = 0; s < nd; ++s) {
+                    const int t = (s + r) % nd;
+                    if (cells[s * nd + t].peer_ok) GP_TRY(launch_pair(s, t, timed));
+                }
+                for (int s = 0; s < nd; ++s) {
+                    const int t = (s + r) % nd;
+                    if (!cells[s * nd + t].peer_ok) continue;
+                    GP_TRY(cudaSetDevice(D[t].ord));
+                    GP_TRY(cudaStreamSynchronize(D[t].st->stream));
+                    if (timed) {
+                        float m = 0;
+                        GP_TRY(cudaEventElapsedTime(&m, D[t].ev0, D[t].ev1));
+                        ms[s].push_back(m);
+                    }
+                }
+            }
+            for (int s = 0; s < nd; ++s) {
+                const int t = (s + r) % nd;
+                if (!cells[s * nd + t].peer_ok) continue;
+                rc = finish_pair(s, t, ms[s]);
+                if (rc) break;
+            }
+        }
+    }
+    cleanup();
+    if (rc) return rc;
+    bool bad = false;
+    for (int s = 0; s < nd; ++s)
+        for (int t = 0; t < nd; ++t)
+            if (s != t && cells[s * nd + t].peer_ok && !cells[s * nd + t].verified) {
+                if (!bad)
+                    set_err(err, errlen, "p2p %d -> %d: checksum %016llx, expected %016llx", cells[s * nd + t].src,
+                            cells[s * nd + t].dst, (unsigned long long)cells[s * nd + t].checksum_got,
+                            (unsigned long long)cells[s * nd + t].checksum_expected);
+                bad = true;
+            }
+    if (bad) return GPUPROBE_FAIL_VERIFY;
+    if (missing_peer) {
+        set_err(err, errlen, "at least one device pair has no peer access");
+        return GPUPROBE_ENOPEER;
+    }
+    return GPUPROBE_OK;
+#undef GP_TRY
+}

@@ -1,0 +1,240 @@
+/*
+ * gpuprobe.h -- C ABI of libgpuprobe.so: B200 (sm_100a) node-validation probes for the
+ * GPU Operator validator.
+ *
+ * The reference has no FFI on this path: its boundary is a process boundary -- the
+ * validator creates a Pod whose init container runs `sh -c vectorAdd`
+ * (reference validator/cuda-workload-validation.yaml:19-20,
+ * validator/plugin-workload-validation.yaml:19-20) and only the exit code is read
+ * (pod phase Succeeded, validator/main.go:1042-1059).  This header is the library a
+ * maintainer would bind from Go with cgo inside that workload container (INTEGRATION.md
+ * shows the stub); each entry point cites the reference behaviour it stands in for.
+ *
+ * Conventions
+ *   return 0   probe ran and passed                        (process exit 0)
+ *   return >0  probe ran and FAILED verification           (GPUPROBE_FAIL_*; exit 1)
+ *   return <0  probe could not run                         (GPUPROBE_E*;     exit 1)
+ *   `err` (may be NULL) receives a NUL-terminated message of at most errlen bytes.
+ *   Nothing is thrown across the ABI and there are no callbacks.  The caller owns every
+ *   struct and buffer it passes.  Unless an entry point says otherwise the library
+ *   allocates the device memory it needs and frees it before returning.  Every entry
+ *   point selects its device itself (safe from any OS thread, e.g. a Go goroutine that
+ *   migrated); calls that use the same device are serialised inside the library.
+ *   There is no CPU fallback: without a usable sm_100 device the compute entry points
+ *   return GPUPROBE_ENODEV / GPUPROBE_EARCH.
+ */
+#ifndef GPUPROBE_H
+#define GPUPROBE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define GPUPROBE_API __attribute__((visibility("default")))
+#else
+#define GPUPROBE_API
+#endif
+
+#define GPUPROBE_ABI_VERSION 1
+
+/* ---- status codes ------------------------------------------------------------- */
+#define GPUPROBE_OK 0
+#define GPUPROBE_FAIL_VERIFY 1   /* output differs from the expected values             */
+#define GPUPROBE_FAIL_BANDWIDTH 2 /* verified, but below the caller's min_frac threshold */
+#define GPUPROBE_EINVAL (-1)     /* bad argument                                        */
+#define GPUPROBE_ENODEV (-2)     /* no such CUDA device / driver not loadable           */
+#define GPUPROBE_EARCH (-3)      /* device is not sm_100 (kernels are sm_100a only)     */
+#define GPUPROBE_ECUDA (-4)      /* a CUDA runtime call failed (message in err)         */
+#define GPUPROBE_ENOMEM (-5)     /* device or pinned-host allocation failed             */
+#define GPUPROBE_ENOPEER (-6)    /* peer access between two devices is unavailable      */
+#define GPUPROBE_ENCCL (-7)      /* NCCL could not be loaded or returned an error       */
+
+/* ---- generator kinds (DESIGN.md "Generator") ------------------------------------ */
+#define GPUPROBE_GEN_UNIT 0 /* a,b uniform in [0,1): what the sample's rand()/RAND_MAX gives */
+#define GPUPROBE_GEN_EDGE 1 /* IEEE-754 edge values: +-0, denormals, +-inf, max finite, ties */
+#define GPUPROBE_GEN_BITS 2 /* arbitrary finite bit patterns                                  */
+
+/* ---- vectorAdd kernel variants (0 = the measured-best default) ------------------- */
+#define GPUPROBE_VADD_AUTO 0
+#define GPUPROBE_VADD_LDG128_U2 1  /* 128-bit ld/st, 2 vectors of each input in flight per thread */
+#define GPUPROBE_VADD_LDG128_U4 2  /* 128-bit ld/st, 4 in flight                                   */
+#define GPUPROBE_VADD_LDG128_U8 3  /* 128-bit ld/st, 8 in flight                                   */
+#define GPUPROBE_VADD_LDG256_U2 4  /* 256-bit ld/st (sm_100 v8.f32), 2 in flight                   */
+#define GPUPROBE_VADD_LDG256_U4 5  /* 256-bit ld/st, 4 in flight                                   */
+#define GPUPROBE_VADD_TMA 6        /* cp.async.bulk ring (16 KiB tiles) through shared memory, one persistent CTA per SM */
+#define GPUPROBE_VADD_PERSIST128 7 /* 128-bit ld/st, grid = k * SM count, grid-stride tiles        */
+#define GPUPROBE_VADD_SCALAR 8     /* 32-bit ld/st; the unaligned / ragged-tail path                */
+#define GPUPROBE_VADD_TMA_8K 9     /* as TMA with 8 KiB tiles, two CTAs per SM                     */
+#define GPUPROBE_VADD_LDG256_U2_EF 10 /* 256-bit ld/st with L2::evict_first on loads and stores    */
+#define GPUPROBE_VADD_NUM_VARIANTS 11
+
+typedef struct gpuprobe_devinfo {
+    char name[128];
+    int cc_major, cc_minor;
+    int sm_count;
+    int mem_clock_khz;
+    int mem_bus_bits;
+    int max_smem_optin; /* bytes of shared memory a CTA can opt in to */
+    uint64_t hbm_bytes;
+    uint64_t l2_bytes;
+} gpuprobe_devinfo;
+
+typedef struct gpuprobe_vadd_cfg {
+    int dev;          /* CUDA ordinal; the sample always used device 0                          */
+    uint64_t n_elems; /* fp32 elements per array; the sample used 50,000 (BASELINE.json cfg 0)  */
+    int iters;        /* timed launches (>=1)                                                   */
+    int warmup;       /* untimed launches before them                                           */
+    uint32_t seed;
+    int gen_kind;     /* GPUPROBE_GEN_*                                                         */
+    int variant;      /* GPUPROBE_VADD_*                                                        */
+    int verify;       /* bit0: digest of C; bit1: on-device regenerate-and-compare (sanity)     */
+    double peak_nominal_gbps;  /* 0 -> 8000 (north_star's nominal B200 HBM figure)              */
+    double peak_measured_gbps; /* 0 -> unknown, frac_measured reported as 0                     */
+} gpuprobe_vadd_cfg;
+
+typedef struct gpuprobe_vadd_result {
+    uint64_t n;
+    uint64_t sum64;      /* sum of the uint32 bit patterns of C, mod 2^64 */
+    uint32_t xor32;      /* xor of the same                               */
+    uint32_t variant;    /* variant that ran                              */
+    uint64_t mismatches; /* elements where C != regenerated a+b (sanity)  */
+    uint64_t algo_bytes; /* 12 * n                                        */
+    double ms_best, ms_median, ms_mean;
+    double gbps_best, gbps_median;
+    double frac_nominal, frac_measured; /* of gbps_median */
+    int l2_resident;     /* 1 if 12*n fits in L2: not an HBM measurement  */
+    int launches;        /* kernel launches per iteration (1, or 2 with a ragged tail) */
+} gpuprobe_vadd_result;
+
+#define GPUPROBE_P2P_SERIAL 0 /* one directed pair at a time                                  */
+#define GPUPROBE_P2P_ROUNDS 1 /* ndev-1 rounds, dst = (src + r) mod ndev, all pairs of a round concurrently */
+
+typedef struct gpuprobe_p2p_cfg {
+    int ndev;
+    const int *devs;         /* NULL -> 0..ndev-1 */
+    uint64_t bytes_per_pair; /* multiple of 16     */
+    int iters, warmup;
+    int mode;                /* GPUPROBE_P2P_*     */
+    uint32_t seed;
+    double peak_gbps;        /* 0 -> 900 (NVLink 5 per direction) */
+} gpuprobe_p2p_cfg;
+
+typedef struct gpuprobe_p2p_cell {
+    int src, dst;       /* CUDA ordinals; data flows src -> dst, the kernel runs on dst */
+    int peer_ok;        /* cudaDeviceCanAccessPeer(dst, src)                            */
+    int verified;       /* checksum_got == checksum_expected && copy intact             */
+    uint64_t checksum_expected, checksum_got; /* sum of uint32 words mod 2^64           */
+    uint32_t xor_expected, xor_got;
+    double ms_best, ms_median;
+    double gbps;        /* bytes_per_pair / ms_median                                   */
+    double frac_of_peak;
+} gpuprobe_p2p_cell;
+
+typedef struct gpuprobe_ar_cfg {
+    int ndev;        /* 2, 4 or 8 (any >= 2 accepted) */
+    const int *devs; /* NULL -> 0..ndev-1              */
+    uint64_t count;  /* int32 elements per rank        */
+    int iters, warmup;
+    uint32_t seed;
+    double peak_gbps; /* 0 -> 900 */
+} gpuprobe_ar_cfg;
+
+typedef struct gpuprobe_ar_result {
+    int ndev;
+    int nccl_version;
+    uint64_t bytes;      /* count * 4 per rank          */
+    uint64_t mismatches; /* over all ranks; must be 0   */
+    double ms_best, ms_median; /* max over ranks per iteration */
+    double algbw_gbps;   /* bytes / ms_median           */
+    double busbw_gbps;   /* algbw * 2(n-1)/n            */
+    double frac_of_peak;
+} gpuprobe_ar_result;
+
+/* ---- library / device queries --------------------------------------------------- */
+
+/* No reference counterpart (the sample binary has no version handshake). */
+GPUPROBE_API int gpuprobe_abi_version(void);
+
+/* Stands in for the sample's implicit cudaGetDeviceCount via cudaMalloc on device 0; the
+ * cuda workload pod sees all GPUs (validator/cuda-workload-validation.yaml:21-25), the
+ * plugin pod the one it was allocated (validator/main.go:973-983). */
+GPUPROBE_API int gpuprobe_device_count(int *n);
+GPUPROBE_API int gpuprobe_device_info(int dev, gpuprobe_devinfo *out);
+GPUPROBE_API const char *gpuprobe_strerror(int code);
+
+/* ---- (a) vectorAdd ---------------------------------------------------------------- */
+
+/* The whole probe: allocate, generate A and B on the device, run C = A + B `warmup+iters`
+ * times, digest and sanity-check C, free.  Replaces the body of the external `vectorAdd`
+ * binary (installed by validator/Dockerfile:33-35,49; run at
+ * validator/cuda-workload-validation.yaml:19-20). */
+GPUPROBE_API int gpuprobe_vectoradd(const gpuprobe_vadd_cfg *cfg, gpuprobe_vadd_result *out, char *err, size_t errlen);
+
+/* Caller-supplied HOST inputs: copies a,b to the device (chunked, pipelined over separate
+ * copy streams), adds, copies C back, so the CALLER's host loop does the bit-exact compare
+ * -- the sample's h_A/h_B -> cudaMemcpy -> kernel -> cudaMemcpy -> h_C sequence.  Pinned
+ * buffers (gpuprobe_host_alloc) are copied directly; pageable ones go through the
+ * library's pinned bounce buffers. */
+GPUPROBE_API int gpuprobe_vectoradd_buffers(int dev, const float *a, const float *b, float *c, uint64_t n, char *err,
+                               size_t errlen);
+
+/* Caller-supplied DEVICE buffers: enqueues the add kernel(s) on `stream` (a cudaStream_t,
+ * NULL = legacy default stream) and returns without synchronising.  Allocates nothing.
+ * This is what bench.py times with CUDA events. */
+GPUPROBE_API int gpuprobe_vectoradd_device(int dev, const float *d_a, const float *d_b, float *d_c, uint64_t n, int variant,
+                              void *stream, char *err, size_t errlen);
+
+/* The deterministic generator on the host, exported so that Go / C++ / Python callers all
+ * produce the inputs the device generator produces (stands in for the sample's
+ * rand()/(float)RAND_MAX fill of h_A, h_B).  a[j], b[j] receive elements first+j. */
+GPUPROBE_API void gpuprobe_fill_inputs(float *a, float *b, uint64_t first, uint64_t n, uint32_t seed, int gen_kind);
+
+/* Same generator on the device, into caller-supplied device buffers (either may be NULL);
+ * asynchronous on `stream`. */
+GPUPROBE_API int gpuprobe_fill_inputs_device(int dev, float *d_a, float *d_b, uint64_t first, uint64_t n, uint32_t seed,
+                                int gen_kind, void *stream, char *err, size_t errlen);
+
+/* sum64 / xor32 of the bit patterns of a device array of n 32-bit words; synchronises
+ * `stream` before returning.  Uses a small device scratch buffer that the library
+ * allocates for the call. */
+GPUPROBE_API int gpuprobe_digest_device(int dev, const void *d_words, uint64_t n, uint64_t *sum64, uint32_t *xor32,
+                           void *stream, char *err, size_t errlen);
+
+/* Counts elements of d_c whose bits differ from regenerated a[first+j] + b[first+j];
+ * synchronises `stream`.  Same adder as the probe, so a sanity check, not parity. */
+GPUPROBE_API int gpuprobe_verify_device(int dev, const float *d_c, uint64_t first, uint64_t n, uint32_t seed, int gen_kind,
+                           uint64_t *mismatches, void *stream, char *err, size_t errlen);
+
+/* Pinned host memory for gpuprobe_vectoradd_buffers callers (cudaHostAlloc / cudaFreeHost). */
+GPUPROBE_API int gpuprobe_host_alloc(void **p, size_t bytes);
+GPUPROBE_API int gpuprobe_host_free(void *p);
+
+/* ---- (b) NVLink P2P all-pairs copy + checksum --------------------------------------- */
+
+/* New capability (the reference never touches a second GPU).  cells is caller-allocated,
+ * ndev*ndev entries, row-major [src][dst]; the diagonal is left zeroed.  Returns
+ * GPUPROBE_FAIL_VERIFY if any pair's checksum is wrong, GPUPROBE_ENOPEER if a pair has
+ * no peer access (its cell has peer_ok = 0). */
+GPUPROBE_API int gpuprobe_p2p_matrix(const gpuprobe_p2p_cfg *cfg, gpuprobe_p2p_cell *cells, char *err, size_t errlen);
+
+/* Expected checksum of source `src`'s buffer, computed on the host (threads <= 0: all). */
+GPUPROBE_API void gpuprobe_p2p_expected(uint64_t nwords, uint32_t seed, int src, int threads, uint64_t *sum64,
+                           uint32_t *xor32);
+
+/* ---- (c) NCCL int32 allreduce fabric check ------------------------------------------ */
+
+/* New capability.  Single process, one communicator over cfg->ndev devices
+ * (ncclCommInitAll); NCCL is loaded at run time (env GPUPROBE_NCCL_LIB, else libnccl.so.2). */
+GPUPROBE_API int gpuprobe_allreduce_i32(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
+
+/* Releases cached per-device state (streams, events, scratch).  Optional. */
+GPUPROBE_API void gpuprobe_shutdown(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPUPROBE_H */

@@ -1,0 +1,52 @@
+"""Fabric probes on real hardware: all-pairs NVLink P2P copy+checksum and the NCCL int32
+allreduce.  Need >= 2 GPUs (gpurun --gpus 2); skipped on a single-GPU box."""
+import pytest
+
+from oracle import oracle as oc
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+
+
+@pytest.fixture(scope="module")
+def ndev(gp):
+    n = gp.device_count()
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    return n
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_p2p_matrix_checksums_match_oracle(gp, ndev, mode):
+    nd = min(ndev, 8)
+    nbytes = (64 << 20) + 16 * 7  # ragged: not a multiple of the kernel's tile
+    rc, cells = gp.p2p_matrix(nd, nbytes, iters=3, warmup=1, mode=mode, seed=3)
+    assert rc == gp.OK
+    for s in range(nd):
+        want = oc.p2p_checksum(nbytes // 4, 3, s)
+        for t in range(nd):
+            c = cells[s][t]
+            assert (c.src, c.dst) == (s, t)
+            if s == t:
+                assert c.gbps == 0
+                continue
+            assert c.peer_ok == 1 and c.verified == 1
+            assert (c.checksum_got, c.xor_got) == want == (c.checksum_expected, c.xor_expected)
+            assert c.gbps > 50, f"{s}->{t}: {c.gbps:.1f} GB/s is not NVLink"
+
+
+def test_p2p_small_and_explicit_device_list(gp, ndev):
+    rc, cells = gp.p2p_matrix(2, 16, iters=1, warmup=0, seed=1, devs=[1, 0])
+    assert rc == gp.OK
+    assert (cells[0][1].src, cells[0][1].dst) == (1, 0)
+    assert (cells[0][1].checksum_got, cells[0][1].xor_got) == oc.p2p_checksum(4, 1, 1)
+    assert (cells[1][0].checksum_got, cells[1][0].xor_got) == oc.p2p_checksum(4, 1, 0)
+    rc, _ = gp.p2p_matrix(2, 1 << 20, devs=[0, 0], raise_on_fail=False)
+    assert rc == gp.EINVAL
+
+
+@pytest.mark.parametrize("count", [1, 1000, (16 << 20) + 5])
+def test_allreduce_int32_bit_exact(gp, ndev, count):
+    for nd in [n for n in (2, 4, 8) if n <= ndev]:
+        res = gp.allreduce_i32(nd, count, iters=3, warmup=2, seed=2)
+        assert res.mismatches == 0 and res.ndev == nd and res.bytes == 4 * count
+        assert res.nccl_version >= 20000
