@@ -385,7 +385,8 @@ verify_kernel(const float *__restrict__ c, uint64_t first, uint64_t n, uint32_t 
 
 // ------------------------------------------------------------------ host: dispatch
 
-constexpr int DEFAULT_VARIANT = GPUPROBE_VADD_LDG128_U4;
+// Measured best on B200 at every HBM-resident size (profiles/r01_vadd_variants.md): the smallest tile.
+constexpr int DEFAULT_VARIANT = GPUPROBE_VADD_LDG128_U1;
 
 struct VariantInfo {
     int vec_floats;  // alignment requirement in floats (0: none)
@@ -394,6 +395,8 @@ struct VariantInfo {
 
 static VariantInfo variant_info(int v) {
     switch (v) {
+    case GPUPROBE_VADD_LDG128_U1: return {4, 256u * 4 * 1};
+    case GPUPROBE_VADD_LDG256_U1: return {8, 256u * 8 * 1};
     case GPUPROBE_VADD_LDG128_U2: return {4, 256u * 4 * 2};
     case GPUPROBE_VADD_LDG128_U4: return {4, 256u * 4 * 4};
     case GPUPROBE_VADD_LDG128_U8: return {4, 256u * 4 * 8};
@@ -451,6 +454,8 @@ int launch_vadd(DeviceState &st, const float *a, const float *b, float *c, uint6
         }
         const dim3 grid(static_cast<unsigned>(n_tiles)), block(VADD_THREADS);
         switch (variant) {
+        case GPUPROBE_VADD_LDG128_U1: vadd_tile_kernel<4, 1, false><<<grid, block, 0, stream>>>(a, b, c); break;
+        case GPUPROBE_VADD_LDG256_U1: vadd_tile_kernel<8, 1, false><<<grid, block, 0, stream>>>(a, b, c); break;
         case GPUPROBE_VADD_LDG128_U2: vadd_tile_kernel<4, 2, false><<<grid, block, 0, stream>>>(a, b, c); break;
         case GPUPROBE_VADD_LDG128_U4: vadd_tile_kernel<4, 4, false><<<grid, block, 0, stream>>>(a, b, c); break;
         case GPUPROBE_VADD_LDG128_U8: vadd_tile_kernel<4, 8, false><<<grid, block, 0, stream>>>(a, b, c); break;

@@ -70,7 +70,9 @@ extern "C" {
 #define GPUPROBE_VADD_SCALAR 8     /* 32-bit ld/st; the unaligned / ragged-tail path                */
 #define GPUPROBE_VADD_TMA_8K 9     /* as TMA with 8 KiB tiles, two CTAs per SM                     */
 #define GPUPROBE_VADD_LDG256_U2_EF 10 /* 256-bit ld/st with L2::evict_first on loads and stores    */
-#define GPUPROBE_VADD_NUM_VARIANTS 11
+#define GPUPROBE_VADD_LDG128_U1 11 /* 128-bit ld/st, 1 vector of each input per thread: 4 KiB tiles  */
+#define GPUPROBE_VADD_LDG256_U1 12 /* 256-bit ld/st, 1 vector of each input per thread: 8 KiB tiles  */
+#define GPUPROBE_VADD_NUM_VARIANTS 13
 
 typedef struct gpuprobe_devinfo {
     char name[128];

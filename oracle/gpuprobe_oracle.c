@@ -80,6 +80,49 @@ void oracle_fill_inputs(float *a, float *b, uint64_t first, uint64_t n, uint32_t
     }
 }
 
+struct fill_job {
+    float *a, *b;
+    uint64_t first, n;
+    uint32_t seed;
+    int kind;
+};
+
+static void *fill_worker(void *p)
+{
+    struct fill_job *j = (struct fill_job *)p;
+    oracle_fill_inputs(j->a, j->b, j->first, j->n, j->seed, j->kind);
+    return NULL;
+}
+
+void oracle_fill_inputs_mt(float *a, float *b, uint64_t first, uint64_t n, uint32_t seed, int kind, int threads)
+{
+    if (threads < 1) threads = 1;
+    if (threads > 256) threads = 256;
+    if (threads == 1 || n < 65536u) {
+        oracle_fill_inputs(a, b, first, n, seed, kind);
+        return;
+    }
+    pthread_t tid[256];
+    struct fill_job job[256];
+    uint64_t per = (n + (uint64_t)threads - 1) / (uint64_t)threads;
+    int started = 0;
+    for (int t = 0; t < threads; ++t) {
+        uint64_t lo = per * (uint64_t)t;
+        if (lo >= n) break;
+        uint64_t hi = lo + per < n ? lo + per : n;
+        job[t].a = a + lo;
+        job[t].b = b + lo;
+        job[t].first = first + lo;
+        job[t].n = hi - lo;
+        job[t].seed = seed;
+        job[t].kind = kind;
+        pthread_create(&tid[t], NULL, fill_worker, &job[t]);
+        ++started;
+    }
+    for (int t = 0; t < started; ++t)
+        pthread_join(tid[t], NULL);
+}
+
 /* --------------------------------------------------------- the host loop */
 
 void oracle_vectoradd(const float *a, const float *b, float *c, uint64_t n)

@@ -54,6 +54,8 @@ uint32_t oracle_gen_bits(uint32_t seed, uint32_t stream, uint64_t i, int kind);
 /* a[j], b[j] for j in [0,n) hold elements first+j */
 void oracle_fill_inputs(float *a, float *b, uint64_t first, uint64_t n, uint32_t seed, int kind);
 
+void oracle_fill_inputs_mt(float *a, float *b, uint64_t first, uint64_t n, uint32_t seed, int kind, int threads);
+
 /* The host loop: c[i] = a[i] + b[i], fp32, one rounding (the "Go host loop" of north_star,
  * the verification loop of the vectorAdd sample). */
 void oracle_vectoradd(const float *a, const float *b, float *c, uint64_t n);

@@ -53,6 +53,8 @@ def lib() -> C.CDLL:
         L.oracle_gen_bits.argtypes = [u32, u32, u64, i32]
         L.oracle_fill_inputs.restype = None
         L.oracle_fill_inputs.argtypes = [fp, fp, u64, u64, u32, i32]
+        L.oracle_fill_inputs_mt.restype = None
+        L.oracle_fill_inputs_mt.argtypes = [fp, fp, u64, u64, u32, i32, i32]
         L.oracle_vectoradd.restype = None
         L.oracle_vectoradd.argtypes = [fp, fp, fp, u64]
         L.oracle_vectoradd_mt.restype = None
@@ -95,10 +97,13 @@ def hash32(seed: int, stream: int, i: int) -> int:
     return int(lib().oracle_hash(seed, stream, i))
 
 
-def fill_inputs(n: int, seed: int = 0, kind: int = GEN_UNIT, first: int = 0):
+def fill_inputs(n: int, seed: int = 0, kind: int = GEN_UNIT, first: int = 0, threads: int = 1):
     a = np.empty(n, dtype=np.float32)
     b = np.empty(n, dtype=np.float32)
-    lib().oracle_fill_inputs(_fp(a), _fp(b), first, n, seed, kind)
+    if threads > 1:
+        lib().oracle_fill_inputs_mt(_fp(a), _fp(b), first, n, seed, kind, threads)
+    else:
+        lib().oracle_fill_inputs(_fp(a), _fp(b), first, n, seed, kind)
     return a, b
 
 

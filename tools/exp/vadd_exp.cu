@@ -1,0 +1,189 @@
+// vadd_exp.cu -- scratch experiments behind the vectorAdd kernel choices (not part of the product).
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo --fmad=false -o tools/exp/bin/vadd_exp tools/exp/vadd_exp.cu
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <functional>
+#include <string>
+#include <vector>
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { fprintf(stderr, "%s: %s\n", #x, cudaGetErrorString(e_)); exit(2); } } while (0)
+
+enum LoadHint { L_NC_NA = 0, L_PLAIN = 1, L_CS = 2, L_LU = 3, L_NC = 4, L_NC_NA_PF256 = 5, L_CG = 6 };
+enum StoreHint { S_NA = 0, S_PLAIN = 1, S_CS = 2, S_WT = 3, S_CG = 4 };
+
+template <int LH> __device__ __forceinline__ float4 ld4(const float *p) {
+    float4 r;
+    if constexpr (LH == L_NC_NA) asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    else if constexpr (LH == L_PLAIN) asm volatile("ld.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    else if constexpr (LH == L_CS) asm volatile("ld.global.cs.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    else if constexpr (LH == L_LU) asm volatile("ld.global.lu.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    else if constexpr (LH == L_NC) asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    else if constexpr (LH == L_NC_NA_PF256) asm volatile("ld.global.nc.L1::no_allocate.L2::256B.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    else asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+template <int SH> __device__ __forceinline__ void st4(float *p, float4 v) {
+    if constexpr (SH == S_NA) asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+    else if constexpr (SH == S_PLAIN) asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+    else if constexpr (SH == S_CS) asm volatile("st.global.cs.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+    else if constexpr (SH == S_WT) asm volatile("st.global.wt.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+    else asm volatile("st.global.cg.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float4 add4(float4 x, float4 y) { return make_float4(__fadd_rn(x.x, y.x), __fadd_rn(x.y, y.y), __fadd_rn(x.z, y.z), __fadd_rn(x.w, y.w)); }
+
+// generic tile kernel: T threads, U float4 per input per thread
+template <int T, int U, int LH, int SH>
+__global__ void __launch_bounds__(T) k_vadd(const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ c) {
+    const size_t base = (size_t)blockIdx.x * (T * U * 4) + threadIdx.x * 4;
+    float4 va[U], vb[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) va[u] = ld4<LH>(a + base + (size_t)u * T * 4);
+#pragma unroll
+    for (int u = 0; u < U; ++u) vb[u] = ld4<LH>(b + base + (size_t)u * T * 4);
+#pragma unroll
+    for (int u = 0; u < U; ++u) st4<SH>(c + base + (size_t)u * T * 4, add4(va[u], vb[u]));
+}
+// 256-bit
+template <int T, int U>
+__global__ void __launch_bounds__(T) k_vadd8(const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ c) {
+    const size_t base = (size_t)blockIdx.x * (T * U * 8) + threadIdx.x * 8;
+    float va[U][8], vb[U][8];
+#pragma unroll
+    for (int u = 0; u < U; ++u) asm volatile("ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=f"(va[u][0]), "=f"(va[u][1]), "=f"(va[u][2]), "=f"(va[u][3]), "=f"(va[u][4]), "=f"(va[u][5]), "=f"(va[u][6]), "=f"(va[u][7]) : "l"(a + base + (size_t)u * T * 8));
+#pragma unroll
+    for (int u = 0; u < U; ++u) asm volatile("ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=f"(vb[u][0]), "=f"(vb[u][1]), "=f"(vb[u][2]), "=f"(vb[u][3]), "=f"(vb[u][4]), "=f"(vb[u][5]), "=f"(vb[u][6]), "=f"(vb[u][7]) : "l"(b + base + (size_t)u * T * 8));
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        float r[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) r[i] = __fadd_rn(va[u][i], vb[u][i]);
+        asm volatile("st.global.L1::no_allocate.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" :: "l"(c + base + (size_t)u * T * 8), "f"(r[0]), "f"(r[1]), "f"(r[2]), "f"(r[3]), "f"(r[4]), "f"(r[5]), "f"(r[6]), "f"(r[7]) : "memory");
+    }
+}
+// read-only (2 streams), write-only, copy
+template <int T, int U>
+__global__ void __launch_bounds__(T) k_read2(const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ c) {
+    const size_t base = (size_t)blockIdx.x * (T * U * 4) + threadIdx.x * 4;
+    float4 acc = make_float4(0, 0, 0, 0);
+#pragma unroll
+    for (int u = 0; u < U; ++u) { float4 x = ld4<L_NC_NA>(a + base + (size_t)u * T * 4), y = ld4<L_NC_NA>(b + base + (size_t)u * T * 4); acc = add4(acc, add4(x, y)); }
+    if (acc.x == 123.456f && acc.y == 1e30f) st4<S_NA>(c + base, acc);
+}
+template <int T, int U>
+__global__ void __launch_bounds__(T) k_write(const float *__restrict__, const float *__restrict__, float *__restrict__ c) {
+    const size_t base = (size_t)blockIdx.x * (T * U * 4) + threadIdx.x * 4;
+#pragma unroll
+    for (int u = 0; u < U; ++u) st4<S_NA>(c + base + (size_t)u * T * 4, make_float4(1.f, 2.f, 3.f, (float)threadIdx.x));
+}
+template <int T, int U>
+__global__ void __launch_bounds__(T) k_copy(const float *__restrict__ a, const float *__restrict__, float *__restrict__ c) {
+    const size_t base = (size_t)blockIdx.x * (T * U * 4) + threadIdx.x * 4;
+    float4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[u] = ld4<L_NC_NA>(a + base + (size_t)u * T * 4);
+#pragma unroll
+    for (int u = 0; u < U; ++u) st4<S_NA>(c + base + (size_t)u * T * 4, v[u]);
+}
+// persistent, chunked: CTA j owns a contiguous run of tiles
+template <int T, int U>
+__global__ void __launch_bounds__(T) k_vadd_chunked(const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ c, size_t n_tiles) {
+    const size_t per = (n_tiles + gridDim.x - 1) / gridDim.x;
+    const size_t lo = per * blockIdx.x, hi = min(lo + per, n_tiles);
+    for (size_t t = lo; t < hi; ++t) {
+        const size_t base = t * (T * U * 4) + threadIdx.x * 4;
+        float4 va[U], vb[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) va[u] = ld4<L_NC_NA>(a + base + (size_t)u * T * 4);
+#pragma unroll
+        for (int u = 0; u < U; ++u) vb[u] = ld4<L_NC_NA>(b + base + (size_t)u * T * 4);
+#pragma unroll
+        for (int u = 0; u < U; ++u) st4<S_NA>(c + base + (size_t)u * T * 4, add4(va[u], vb[u]));
+    }
+}
+
+struct Exp { std::string name; double bytes_per_elem; std::function<void(const float *, const float *, float *, size_t, cudaStream_t)> run; };
+
+template <int T, int U, int LH, int SH> Exp mk(const char *name) {
+    return {name, 12, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd<T, U, LH, SH><<<(unsigned)(n / (T * U * 4)), T, 0, s>>>(a, b, c); }};
+}
+template <int T, int U> Exp mk8(const char *name) {
+    return {name, 12, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd8<T, U><<<(unsigned)(n / (T * U * 8)), T, 0, s>>>(a, b, c); }};
+}
+
+int main(int argc, char **argv) {
+    int lg = argc > 1 ? atoi(argv[1]) : 30;
+    int iters = argc > 2 ? atoi(argv[2]) : 20;
+    const char *filter = argc > 3 ? argv[3] : "";
+    const size_t n = (size_t)1 << lg;
+    const size_t PAD = 64u << 20;  // room for offset experiments
+    char *pool;
+    CK(cudaMalloc(&pool, 3 * (n * 4 + PAD)));
+    CK(cudaMemset(pool, 0, 3 * (n * 4 + PAD)));
+    cudaStream_t s; CK(cudaStreamCreate(&s));
+    int sms; CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
+
+    std::vector<Exp> E;
+    E.push_back({"read2_t256_u2", 8, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_read2<256, 2><<<(unsigned)(n / (256 * 2 * 4)), 256, 0, s>>>(a, b, c); }});
+    E.push_back({"write_t256_u2", 4, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_write<256, 2><<<(unsigned)(n / (256 * 2 * 4)), 256, 0, s>>>(a, b, c); }});
+    E.push_back({"copy_t256_u2", 8, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_copy<256, 2><<<(unsigned)(n / (256 * 2 * 4)), 256, 0, s>>>(a, b, c); }});
+    E.push_back(mk<256, 2, L_NC_NA, S_NA>("vadd_t256_u2"));
+    E.push_back(mk<256, 1, L_NC_NA, S_NA>("vadd_t256_u1"));
+    E.push_back(mk<512, 1, L_NC_NA, S_NA>("vadd_t512_u1"));
+    E.push_back(mk<1024, 1, L_NC_NA, S_NA>("vadd_t1024_u1"));
+    E.push_back(mk<128, 1, L_NC_NA, S_NA>("vadd_t128_u1"));
+    E.push_back(mk<128, 2, L_NC_NA, S_NA>("vadd_t128_u2"));
+    E.push_back(mk<512, 2, L_NC_NA, S_NA>("vadd_t512_u2"));
+    E.push_back(mk<64, 2, L_NC_NA, S_NA>("vadd_t64_u2"));
+    E.push_back(mk<64, 4, L_NC_NA, S_NA>("vadd_t64_u4"));
+    E.push_back(mk8<128, 1>("vadd8_t128_u1"));
+    E.push_back(mk8<256, 1>("vadd8_t256_u1"));
+    E.push_back(mk8<512, 1>("vadd8_t512_u1"));
+    E.push_back(mk<256, 2, L_PLAIN, S_NA>("vadd_ldplain"));
+    E.push_back(mk<256, 2, L_CS, S_NA>("vadd_ldcs"));
+    E.push_back(mk<256, 2, L_LU, S_NA>("vadd_ldlu"));
+    E.push_back(mk<256, 2, L_NC, S_NA>("vadd_ldnc"));
+    E.push_back(mk<256, 2, L_CG, S_NA>("vadd_ldcg"));
+    E.push_back(mk<256, 2, L_NC_NA_PF256, S_NA>("vadd_ldpf256"));
+    E.push_back(mk<256, 2, L_NC_NA, S_PLAIN>("vadd_stplain"));
+    E.push_back(mk<256, 2, L_NC_NA, S_CS>("vadd_stcs"));
+    E.push_back(mk<256, 2, L_NC_NA, S_WT>("vadd_stwt"));
+    E.push_back(mk<256, 2, L_NC_NA, S_CG>("vadd_stcg"));
+    E.push_back(mk<256, 2, L_CS, S_CS>("vadd_ldcs_stcs"));
+    for (int k : {1, 2, 4, 8, 16})
+        E.push_back({"chunked_x" + std::to_string(k), 12, [k, sms](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd_chunked<256, 2><<<sms * k, 256, 0, s>>>(a, b, c, n / 2048); }});
+
+    // base-pointer offsets between the three arrays (bytes)
+    struct Off { const char *name; size_t a, b, c; };
+    std::vector<Off> offs = {{"off0", 0, 0, 0}};
+    if (std::string(filter) == "offsets" || std::string(filter) == "all")
+        offs = {{"off0", 0, 0, 0}, {"off_4k", 0, 4096, 8192}, {"off_64k", 0, 65536, 131072}, {"off_1m", 0, 1u << 20, 2u << 20},
+                {"off_1m4k", 0, (1u << 20) + 4096, (2u << 20) + 8192}, {"off_odd", 0, 7u * 4096 + 512, 13u * 65536 + 1024}, {"off_32m", 0, 32u << 20, 16u << 20}};
+
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    for (auto &o : offs) {
+        float *a = (float *)(pool + o.a), *b = (float *)(pool + (n * 4 + PAD) + o.b), *c = (float *)(pool + 2 * (n * 4 + PAD) + o.c);
+        for (auto &x : E) {
+            if (*filter && std::string(filter) != "all" && std::string(filter) != "offsets" && x.name.find(filter) == std::string::npos) continue;
+            if (std::string(filter) == "offsets" && x.name != "vadd_t256_u2") continue;
+            for (int i = 0; i < 3; ++i) x.run(a, b, c, n, s);
+            CK(cudaGetLastError());
+            std::vector<float> ms(iters);
+            for (int i = 0; i < iters; ++i) {
+                CK(cudaEventRecord(e0, s));
+                x.run(a, b, c, n, s);
+                CK(cudaEventRecord(e1, s));
+                CK(cudaEventSynchronize(e1));
+                CK(cudaEventElapsedTime(&ms[i], e0, e1));
+            }
+            std::sort(ms.begin(), ms.end());
+            double med = ms[iters / 2], best = ms[0];
+            printf("{\"exp\": \"%s\", \"offs\": \"%s\", \"log2n\": %d, \"ms_median\": %.5f, \"gbps_median\": %.1f, \"gbps_best\": %.1f}\n", x.name.c_str(), o.name, lg, med,
+                   x.bytes_per_elem * n / (med * 1e6), x.bytes_per_elem * n / (best * 1e6));
+            fflush(stdout);
+        }
+    }
+    return 0;
+}
