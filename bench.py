@@ -44,7 +44,7 @@ METRIC = "vectorAdd HBM GB/s"
 UNIT = "GB/s"
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the default kernel at n = 2^30,
 # from the ncu --set full capture summarised in profiles/r01_vadd_ncu_full.md
-NCU_TRAFFIC_BYTES_2P30 = 12_847_855_000
+NCU_TRAFFIC_BYTES_2P30 = 12_850_400_000
 CPU_SAMPLE_LOG2 = 28
 
 
