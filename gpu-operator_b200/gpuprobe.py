@@ -111,6 +111,7 @@ SIGNATURES = {
     "gpuprobe_fill_inputs": (None, [C.c_void_p, C.c_void_p, _u64, _u64, _u32, _int]),
     "gpuprobe_fill_inputs_device": (_int, [_int, C.c_void_p, C.c_void_p, _u64, _u64, _u32, _int, C.c_void_p, *_err]),
     "gpuprobe_digest_device": (_int, [_int, C.c_void_p, _u64, C.POINTER(_u64), C.POINTER(_u32), C.c_void_p, *_err]),
+    "gpuprobe_digest_device_noalloc": (_int, [_int, C.c_void_p, _u64, C.POINTER(_u64), C.POINTER(_u32), C.c_void_p, *_err]),
     "gpuprobe_verify_device": (_int, [_int, C.c_void_p, _u64, _u64, _u32, _int, C.POINTER(_u64), C.c_void_p, *_err]),
     "gpuprobe_host_alloc": (_int, [C.POINTER(C.c_void_p), C.c_size_t]),
     "gpuprobe_host_free": (_int, [C.c_void_p]),
@@ -213,6 +214,18 @@ def digest_device(d_words, n: int, dev: int = 0, stream: int = 0):
     s, x, eb = _u64(0), _u32(0), _errbuf()
     _check(lib.gpuprobe_digest_device(dev, _ptr(d_words), n, C.byref(s), C.byref(x), stream, eb, len(eb)),
            "gpuprobe_digest_device", eb)
+    return s.value, x.value
+
+
+NOALLOC_MAX_WORDS = 1 << 30
+
+
+def digest_device_noalloc(d_words, n: int, dev: int = 0, stream: int = 0):
+    """gpuprobe_digest_device_noalloc: same result as digest_device, but no device allocation
+    (fixed in-library scratch; at most NOALLOC_MAX_WORDS words per call)."""
+    s, x, eb = _u64(0), _u32(0), _errbuf()
+    _check(lib.gpuprobe_digest_device_noalloc(dev, _ptr(d_words), n, C.byref(s), C.byref(x), stream, eb, len(eb)),
+           "gpuprobe_digest_device_noalloc", eb)
     return s.value, x.value
 
 

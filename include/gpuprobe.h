@@ -206,6 +206,24 @@ GPUPROBE_API int gpuprobe_fill_inputs_device(int dev, float *d_a, float *d_b, ui
 GPUPROBE_API int gpuprobe_digest_device(int dev, const void *d_words, uint64_t n, uint64_t *sum64, uint32_t *xor32,
                            void *stream, char *err, size_t errlen);
 
+/* The same digest for callers that must not allocate: a re-check that runs while tenant jobs
+ * hold (nearly) all of HBM or the whole MIG slice, and any caller that may not disturb those
+ * jobs -- cudaMalloc/cudaFree take device-wide locks and cudaFree waits for the device to
+ * idle -- or that lives inside a framework's memory pool and may not go around it.
+ * No counterpart in the reference (which never inspects device data at all).
+ * Scratch is a fixed GPUPROBE_NOALLOC_SCRATCH_BYTES array inside the library image, resident on
+ * every GPU that loads the library until the process exits.  It allows at most
+ * GPUPROBE_NOALLOC_MAX_WORDS words per call; more is rejected with GPUPROBE_EINVAL.  The call
+ * performs no cudaMalloc/cudaFree, clears the 16 bytes of state that must start at zero on
+ * `stream`, launches, copies the 16-byte result back and synchronises `stream`.  All calls on
+ * a device share the array: the library serialises them, and work that reads the array must
+ * not overlap on the GPU.  The first call on each device looks the array's address up (set-up);
+ * make that first call outside any stream capture. */
+#define GPUPROBE_NOALLOC_MAX_WORDS (1ull << 30)
+#define GPUPROBE_NOALLOC_SCRATCH_BYTES 196864
+GPUPROBE_API int gpuprobe_digest_device_noalloc(int dev, const void *d_words, uint64_t n, uint64_t *sum64,
+                                                uint32_t *xor32, void *stream, char *err, size_t errlen);
+
 /* Counts elements of d_c whose bits differ from regenerated a[first+j] + b[first+j];
  * synchronises `stream`.  Same adder as the probe, so a sanity check, not parity. */
 GPUPROBE_API int gpuprobe_verify_device(int dev, const float *d_c, uint64_t first, uint64_t n, uint32_t seed, int gen_kind,
