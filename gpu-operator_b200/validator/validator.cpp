@@ -571,7 +571,10 @@ static std::string runWorkload(Runtime &rt, const char *specPath, const char *wh
     std::string name;
     e = rt.launcher->create(pod, &name);
     if (!e.empty()) return sprintfStr("failed to create %s validation pod %s, err %s", what, pod.generateName.c_str(), e.c_str());
-    return waitForPod(*rt.launcher, name, podCreationWaitRetries, rt.pollMillis);
+    int retries = podCreationWaitRetries;
+    if (!rt.keepRetryCounts && rt.pollMillis > 0 && rt.pollMillis < podCreationSleepIntervalSeconds * 1000)
+        retries = podCreationWaitRetries * (podCreationSleepIntervalSeconds * 1000 / rt.pollMillis);
+    return waitForPod(*rt.launcher, name, retries, rt.pollMillis);
 }
 
 std::string validateCUDA(Runtime &rt) {
@@ -583,7 +586,10 @@ std::string validateCUDA(Runtime &rt) {
 }
 
 static std::string validateGPUResource(Runtime &rt) {
-    for (int retry = 1; retry <= gpuResourceDiscoveryWaitRetries; ++retry) {
+    int retries = gpuResourceDiscoveryWaitRetries;
+    if (!rt.keepRetryCounts && rt.discoveryPollMillis > 0 && rt.discoveryPollMillis < gpuResourceDiscoveryIntervalSeconds * 1000)
+        retries = gpuResourceDiscoveryWaitRetries * (gpuResourceDiscoveryIntervalSeconds * 1000 / rt.discoveryPollMillis);
+    for (int retry = 1; retry <= retries; ++retry) {
         ResourceList cap, alloc;
         std::string e = rt.node->get(&cap, &alloc);
         if (!e.empty())

@@ -133,6 +133,9 @@ struct Runtime {
     std::unique_ptr<NodeResources> node;
     int pollMillis = podCreationSleepIntervalSeconds * 1000;
     int discoveryPollMillis = gpuResourceDiscoveryIntervalSeconds * 1000;
+    // A shorter poll keeps the reference's time budgets (60 x 5 s, 30 x 5 s) by scaling the retry
+    // counts, unless keepRetryCounts asks for the reference's counts verbatim (tests).
+    bool keepRetryCounts = false;
     std::string manifestDir;  // "" -> the reference's absolute paths
 };
 std::string validateCUDA(Runtime &rt);     // CUDA.validate   main.go:1176-1211

@@ -4,6 +4,7 @@
 //   GPUPROBE_MANIFEST_DIR   directory holding cuda-/plugin-workload-validation.yaml
 //                           (default: the reference's /var/nvidia/manifests)
 //   GPUPROBE_POLL_MS        pod-phase poll period in ms (reference: 5000, main.go:161)
+//   GPUPROBE_KEEP_RETRY_COUNTS=1  with a shorter poll, keep 60/30 retries instead of the 300 s/150 s budgets
 //   GPUPROBE_BIN_DIR        prepended to the workload's PATH so that `vectorAdd` resolves
 #include <signal.h>
 #include <unistd.h>
@@ -38,6 +39,7 @@ int main(int argc, char **argv) {
             int ms = atoi(p);
             if (ms > 0) rt.pollMillis = rt.discoveryPollMillis = ms;
         }
+        if (const char *k = getenv("GPUPROBE_KEEP_RETRY_COUNTS")) rt.keepRetryCounts = (*k == '1');
         err = start(rt);
     }
     if (!err.empty()) {

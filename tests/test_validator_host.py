@@ -56,7 +56,7 @@ def built():
 
 
 def run(args=(), env=None, timeout=60):
-    e = {"PATH": os.environ["PATH"], "GPUPROBE_POLL_MS": "5", "SLEEP_INTERVAL_SECONDS": "0"}
+    e = {"PATH": os.environ["PATH"], "GPUPROBE_POLL_MS": "5", "GPUPROBE_KEEP_RETRY_COUNTS": "1", "SLEEP_INTERVAL_SECONDS": "0"}
     e.update(env or {})
     return subprocess.run([VALIDATOR, *args], env=e, capture_output=True, text=True, timeout=timeout)
 
