@@ -386,9 +386,13 @@ def main() -> int:
                     fabric["p2p_rounds"] = {"rc": rc, "min_gbps": round(min(g), 1), "median_gbps": round(statistics.median(g), 1),
                                             "max_gbps": round(max(g), 1)}
                     ar = gp.allreduce_i32(world, 1 << 28, iters=10, warmup=3)
-                    fabric["allreduce_i32"] = {"ndev": world, "bytes": ar.bytes, "mismatches": ar.mismatches,
-                                               "busbw_gbps": round(ar.busbw_gbps, 1), "algbw_gbps": round(ar.algbw_gbps, 1),
-                                               "frac_of_900": round(ar.frac_of_peak, 4), "nccl_version": ar.nccl_version}
+                    fabric["allreduce_i32_nccl"] = {"ndev": world, "bytes": ar.bytes, "mismatches": ar.mismatches,
+                                                    "busbw_gbps": round(ar.busbw_gbps, 1), "algbw_gbps": round(ar.algbw_gbps, 1),
+                                                    "frac_of_900": round(ar.frac_of_peak, 4), "nccl_version": ar.nccl_version}
+                    nv = gp.allreduce_i32_nvls(world, 1 << 28, iters=10, warmup=3)
+                    fabric["allreduce_i32_nvls_kernel"] = {"ndev": world, "bytes": nv.bytes, "mismatches": nv.mismatches,
+                                                           "busbw_gbps": round(nv.busbw_gbps, 1), "algbw_gbps": round(nv.algbw_gbps, 1),
+                                                           "frac_of_900": round(nv.frac_of_peak, 4)}
                 except gp.GpuProbeError as e:
                     fabric["error"] = str(e)
                 line["fabric"] = fabric

@@ -1,0 +1,476 @@
+// nvls.cu -- probe (c'): int32 allreduce as ONE kernel per GPU over NVLink multicast (NVLS).
+//
+// The NCCL probe (allreduce.cu) validates the library path. This one exercises the switch itself:
+// every GPU's buffer is bound to one multicast object, and a single cooperative kernel per GPU does
+//
+//     fill (optional)  x_r[i] = (int32)hash(seed, AR(r), i)          local stores
+//     barrier          multimem.red.release.sys on a flag word + ld.acquire.sys spin
+//     reduce+broadcast for i in my 1/n slice:  v = multimem.ld_reduce.add.u32 [mc + i]   (NVSwitch pulls the word from
+//                                               all n GPUs and adds in the switch)
+//                                              multimem.st.u32 [mc + i], v                (NVSwitch writes v to all n GPUs)
+//     barrier
+//     verify (optional) compare every local word with mult * sum_r hash(seed, AR(r), i)
+//
+// so the transfer and the arithmetic are the same instructions; there is no separate compute step and no
+// staging copy. Per GPU roughly count*4*(1 + 1/n) bytes leave and the same arrive, against 2(n-1)/n * count*4 each
+// way for a ring, which is why busbw (= algbw * 2(n-1)/n) can exceed the 900 GB/s link figure.
+//
+// The reference has no counterpart.
+//
+// Driver-API calls (cuMem*, cuMulticast*) are resolved with cudaGetDriverEntryPoint, so the library still has
+// no link-time dependency on libcuda. Cross-GPU spins have a timeout and raise an error flag instead of hanging.
+#include <cooperative_groups.h>
+#include <cuda.h>
+
+#include "common.cuh"
+#include "gen.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace gp {
+
+constexpr int NVLS_THREADS = 512;
+constexpr uint64_t NVLS_FLAG_BYTES = 4096;  // the flag word lives in its own page-slice behind the payload
+constexpr unsigned long long NVLS_SPIN_TIMEOUT_NS = 4000000000ull;
+
+enum : int { NVLS_FILL = 1, NVLS_REDUCE = 2, NVLS_VERIFY = 4 };
+
+struct NvlsArgs {
+    uint32_t *local;        // unicast mapping of this rank's buffer
+    uint32_t *mc;           // multicast mapping of the same bytes on every rank
+    uint32_t *flag_local;   // unicast address of the barrier word in this rank's memory
+    uint32_t *flag_mc;      // multicast address of the barrier word
+    unsigned long long *mismatches;
+    int *error;             // set to 1 if a cross-GPU wait timed out
+    uint64_t count;
+    uint32_t seed;
+    uint32_t mult;          // verify: expected = mult * sum_r x_r[i]
+    uint32_t barrier_base;  // number of barriers completed before this launch
+    int rank, nranks, phases;
+};
+
+__device__ __forceinline__ uint32_t mm_ld_reduce_add_u32(const uint32_t *mc) {
+    uint32_t v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u32 %0, [%1];" : "=r"(v) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void mm_st_u32(uint32_t *mc, uint32_t v) {
+    asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(mc), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// All CTAs of all ranks meet here. Local arrival is the cooperative grid barrier; one thread then adds 1 to the
+// flag word of EVERY rank through the multicast address (release at system scope, so everything this grid wrote
+// before is visible to whoever acquires the flag) and waits until its own copy shows that all ranks did the same.
+__device__ void cross_gpu_barrier(cg::grid_group &grid, const NvlsArgs &a, uint32_t index) {
+    grid.sync();
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        __threadfence_system();
+        asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" ::"l"(a.flag_mc), "r"(1u) : "memory");
+        const uint32_t target = (a.barrier_base + index + 1u) * static_cast<uint32_t>(a.nranks);
+        const unsigned long long t0 = globaltimer_ns();
+        for (;;) {
+            uint32_t seen;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.flag_local) : "memory");
+            if (static_cast<int32_t>(seen - target) >= 0) break;
+            if (globaltimer_ns() - t0 > NVLS_SPIN_TIMEOUT_NS) {
+                *a.error = 1;
+                break;
+            }
+            __nanosleep(200);
+        }
+        __threadfence_system();
+    }
+    grid.sync();
+}
+
+template <int NVLS_UNROLL>
+__global__ void __launch_bounds__(NVLS_THREADS) nvls_allreduce_kernel(NvlsArgs a) {
+    cg::grid_group grid = cg::this_grid();
+    const uint64_t gtid = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const uint64_t gstride = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+    uint32_t bar = 0;
+
+    if (a.phases & NVLS_FILL) {
+        const uint32_t base = hash_base(a.seed, stream_ar(a.rank));
+        const uint64_t groups = a.count / 4;
+        for (uint64_t g = gtid; g < groups; g += gstride) {
+            const uint64_t j = g * 4;
+            stg128_stream(a.local + j, make_uint4(hash_at(base, j), hash_at(base, j + 1), hash_at(base, j + 2), hash_at(base, j + 3)));
+        }
+        for (uint64_t j = groups * 4 + gtid; j < a.count; j += gstride) a.local[j] = hash_at(base, j);
+    }
+
+    if (a.phases & NVLS_REDUCE) {
+        cross_gpu_barrier(grid, a, bar++);  // every rank's inputs are in place (and last round's stores have landed)
+        // my slice, rounded so that warps stay on 128-byte lines
+        uint64_t per = (a.count + a.nranks - 1) / a.nranks;
+        per = (per + 31) & ~31ull;
+        const uint64_t lo = min(per * a.rank, a.count), hi = min(lo + per, a.count);
+        constexpr uint64_t TILE = static_cast<uint64_t>(NVLS_THREADS) * NVLS_UNROLL;
+        const uint64_t n_tiles = (hi - lo) / TILE;
+        for (uint64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+            const uint64_t base = lo + t * TILE + threadIdx.x;
+            uint32_t v[NVLS_UNROLL];
+#pragma unroll
+            for (int u = 0; u < NVLS_UNROLL; ++u) v[u] = mm_ld_reduce_add_u32(a.mc + base + u * NVLS_THREADS);
+#pragma unroll
+            for (int u = 0; u < NVLS_UNROLL; ++u) mm_st_u32(a.mc + base + u * NVLS_THREADS, v[u]);
+        }
+        for (uint64_t i = lo + n_tiles * TILE + gtid; i < hi; i += gstride) mm_st_u32(a.mc + i, mm_ld_reduce_add_u32(a.mc + i));
+        cross_gpu_barrier(grid, a, bar++);  // every slice has been broadcast
+    }
+
+    if (a.phases & NVLS_VERIFY) {
+        unsigned long long bad = 0;
+        for (uint64_t i = gtid; i < a.count; i += gstride) {
+            uint32_t s = 0;
+            for (int r = 0; r < a.nranks; ++r) s += hash(a.seed, stream_ar(r), i);
+            uint32_t got;
+            asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(got) : "l"(a.local + i) : "memory");  // written by peers: skip L1
+            bad += (s * a.mult != got);
+        }
+        bad = warp_sum_u64(bad);
+        if ((threadIdx.x & 31) == 0 && bad) atomicAdd(a.mismatches, bad);
+    }
+}
+
+// ---- driver entry points, resolved at run time -------------------------------------------------------------
+struct DriverApi {
+    bool ok = false;
+    CUresult (*GetErrorString)(CUresult, const char **) = nullptr;
+    CUresult (*DeviceGetAttribute)(int *, CUdevice_attribute, CUdevice) = nullptr;
+    CUresult (*DeviceGet)(CUdevice *, int) = nullptr;
+    CUresult (*MemCreate)(CUmemGenericAllocationHandle *, size_t, const CUmemAllocationProp *, unsigned long long) = nullptr;
+    CUresult (*MemRelease)(CUmemGenericAllocationHandle) = nullptr;
+    CUresult (*MemAddressReserve)(CUdeviceptr *, size_t, size_t, CUdeviceptr, unsigned long long) = nullptr;
+    CUresult (*MemAddressFree)(CUdeviceptr, size_t) = nullptr;
+    CUresult (*MemMap)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long) = nullptr;
+    CUresult (*MemUnmap)(CUdeviceptr, size_t) = nullptr;
+    CUresult (*MemSetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc *, size_t) = nullptr;
+    CUresult (*MemGetAllocationGranularity)(size_t *, const CUmemAllocationProp *, CUmemAllocationGranularity_flags) = nullptr;
+    CUresult (*MulticastCreate)(CUmemGenericAllocationHandle *, const CUmulticastObjectProp *) = nullptr;
+    CUresult (*MulticastAddDevice)(CUmemGenericAllocationHandle, CUdevice) = nullptr;
+    CUresult (*MulticastBindMem)(CUmemGenericAllocationHandle, size_t, CUmemGenericAllocationHandle, size_t, size_t, unsigned long long) = nullptr;
+    CUresult (*MulticastUnbind)(CUmemGenericAllocationHandle, CUdevice, size_t, size_t) = nullptr;
+    CUresult (*MulticastGetGranularity)(size_t *, const CUmulticastObjectProp *, CUmulticastGranularity_flags) = nullptr;
+};
+static DriverApi g_drv;
+static std::mutex g_drv_mu;
+
+static int load_driver(char *err, size_t errlen) {
+    std::lock_guard<std::mutex> lock(g_drv_mu);
+    if (g_drv.ok) return GPUPROBE_OK;
+    DriverApi d;
+#define GP_DRV(field, name)                                                                              \
+    {                                                                                                    \
+        void *fn = nullptr;                                                                              \
+        cudaDriverEntryPointQueryResult q;                                                               \
+        cudaError_t e = cudaGetDriverEntryPoint(name, &fn, cudaEnableDefault, &q);                       \
+        if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || !fn) {                               \
+            (void)cudaGetLastError();                                                                    \
+            set_err(err, errlen, "driver entry point %s unavailable", name);                             \
+            return GPUPROBE_ECUDA;                                                                       \
+        }                                                                                                \
+        d.field = reinterpret_cast<decltype(d.field)>(fn);                                               \
+    }
+    GP_DRV(GetErrorString, "cuGetErrorString")
+    GP_DRV(DeviceGetAttribute, "cuDeviceGetAttribute")
+    GP_DRV(DeviceGet, "cuDeviceGet")
+    GP_DRV(MemCreate, "cuMemCreate")
+    GP_DRV(MemRelease, "cuMemRelease")
+    GP_DRV(MemAddressReserve, "cuMemAddressReserve")
+    GP_DRV(MemAddressFree, "cuMemAddressFree")
+    GP_DRV(MemMap, "cuMemMap")
+    GP_DRV(MemUnmap, "cuMemUnmap")
+    GP_DRV(MemSetAccess, "cuMemSetAccess")
+    GP_DRV(MemGetAllocationGranularity, "cuMemGetAllocationGranularity")
+    GP_DRV(MulticastCreate, "cuMulticastCreate")
+    GP_DRV(MulticastAddDevice, "cuMulticastAddDevice")
+    GP_DRV(MulticastBindMem, "cuMulticastBindMem")
+    GP_DRV(MulticastUnbind, "cuMulticastUnbind")
+    GP_DRV(MulticastGetGranularity, "cuMulticastGetGranularity")
+#undef GP_DRV
+    d.ok = true;
+    g_drv = d;
+    return GPUPROBE_OK;
+}
+
+struct NvlsDev {
+    int ord = -1;
+    DeviceState *st = nullptr;
+    CUmemGenericAllocationHandle mem = 0;
+    CUdeviceptr uc = 0;  // unicast mapping
+    bool uc_mapped = false, bound = false;
+    unsigned long long *bad = nullptr;
+    int *error = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int grid = 0;
+};
+
+}  // namespace gp
+
+using namespace gp;
+
+extern "C" int gpuprobe_allreduce_i32_nvls(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen) {
+    if (!cfg || !out) {
+        set_err(err, errlen, "null cfg/out");
+        return GPUPROBE_EINVAL;
+    }
+    std::memset(out, 0, sizeof(*out));
+    const int nd = cfg->ndev;
+    if (nd < 2 || nd > MAX_DEVICES || cfg->count == 0 || cfg->iters < 1 || cfg->warmup < 0) {
+        set_err(err, errlen, "bad allreduce cfg: ndev=%d count=%llu iters=%d warmup=%d", nd,
+                (unsigned long long)cfg->count, cfg->iters, cfg->warmup);
+        return GPUPROBE_EINVAL;
+    }
+    std::vector<NvlsDev> D(nd);
+    int rc;
+    for (int i = 0; i < nd; ++i) {
+        D[i].ord = cfg->devs ? cfg->devs[i] : i;
+        for (int j = 0; j < i; ++j)
+            if (D[j].ord == D[i].ord) {
+                set_err(err, errlen, "device %d listed twice", D[i].ord);
+                return GPUPROBE_EINVAL;
+            }
+        rc = use_device(D[i].ord, &D[i].st, err, errlen);
+        if (rc) return rc;
+    }
+    rc = load_driver(err, errlen);
+    if (rc) return rc;
+    for (auto &d : D) {
+        int mc = 0;
+        if (g_drv.DeviceGetAttribute(&mc, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, d.ord) != CUDA_SUCCESS || !mc) {
+            set_err(err, errlen, "device %d does not support NVLink multicast (NVLS)", d.ord);
+            return GPUPROBE_ENOPEER;
+        }
+    }
+    std::vector<int> order(nd);
+    for (int i = 0; i < nd; ++i) order[i] = i;
+    std::sort(order.begin(), order.end(), [&](int x, int y) { return D[x].ord < D[y].ord; });
+    std::vector<std::unique_lock<std::mutex>> locks;
+    for (int i : order) locks.emplace_back(D[i].st->mu);
+
+    // tuning knobs (defaults are the measured best; see profiles/)
+    int unroll = 8, ctas_per_sm = 2;
+    if (const char *u = getenv("GPUPROBE_NVLS_UNROLL")) unroll = atoi(u);
+    if (const char *c = getenv("GPUPROBE_NVLS_CTAS")) ctas_per_sm = std::max(1, atoi(c));
+    const void *kernel_fn = unroll >= 16  ? reinterpret_cast<const void *>(nvls_allreduce_kernel<16>)
+                            : unroll >= 8 ? reinterpret_cast<const void *>(nvls_allreduce_kernel<8>)
+                            : unroll >= 4 ? reinterpret_cast<const void *>(nvls_allreduce_kernel<4>)
+                                          : reinterpret_cast<const void *>(nvls_allreduce_kernel<2>);
+
+    const uint64_t payload = cfg->count * sizeof(uint32_t);
+    CUmemGenericAllocationHandle mc_handle = 0;
+    CUdeviceptr mc_va = 0;
+    bool mc_created = false, mc_mapped = false;
+    size_t size = 0;
+
+    auto cleanup = [&]() {
+        for (auto &d : D) {
+            if (cudaSetDevice(d.ord) != cudaSuccess) continue;
+            cudaDeviceSynchronize();
+            cudaFree(d.bad);
+            cudaFree(d.error);
+            if (d.ev0) cudaEventDestroy(d.ev0);
+            if (d.ev1) cudaEventDestroy(d.ev1);
+        }
+        if (mc_mapped) g_drv.MemUnmap(mc_va, size);
+        if (mc_va) g_drv.MemAddressFree(mc_va, size);
+        for (auto &d : D) {
+            if (d.bound) g_drv.MulticastUnbind(mc_handle, d.ord, 0, size);
+            if (d.uc_mapped) g_drv.MemUnmap(d.uc, size);
+            if (d.uc) g_drv.MemAddressFree(d.uc, size);
+            if (d.mem) g_drv.MemRelease(d.mem);
+        }
+        if (mc_created) g_drv.MemRelease(mc_handle);
+        (void)cudaGetLastError();
+    };
+#define GP_TRY(call)                                                                                   \
+    do {                                                                                               \
+        cudaError_t e_ = (call);                                                                       \
+        if (e_ != cudaSuccess) {                                                                       \
+            set_err(err, errlen, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            (void)cudaGetLastError();                                                                  \
+            cleanup();                                                                                 \
+            return e_ == cudaErrorMemoryAllocation ? GPUPROBE_ENOMEM : GPUPROBE_ECUDA;                 \
+        }                                                                                              \
+    } while (0)
+#define GP_DRVTRY(call)                                                                                \
+    do {                                                                                               \
+        CUresult r_ = (call);                                                                          \
+        if (r_ != CUDA_SUCCESS) {                                                                      \
+            const char *s_ = "?";                                                                      \
+            g_drv.GetErrorString(r_, &s_);                                                             \
+            set_err(err, errlen, "%s failed: %s (%s:%d)", #call, s_, __FILE__, __LINE__);              \
+            cleanup();                                                                                 \
+            return r_ == CUDA_ERROR_OUT_OF_MEMORY ? GPUPROBE_ENOMEM : GPUPROBE_ECUDA;                  \
+        }                                                                                              \
+    } while (0)
+
+    // one multicast object over all ranks; every rank binds a physical allocation of the same size
+    CUmulticastObjectProp mp;
+    std::memset(&mp, 0, sizeof(mp));
+    mp.numDevices = static_cast<unsigned>(nd);
+    mp.handleTypes = CU_MEM_HANDLE_TYPE_NONE;
+    mp.size = payload + NVLS_FLAG_BYTES;
+    size_t gran = 0;
+    GP_DRVTRY(g_drv.MulticastGetGranularity(&gran, &mp, CU_MULTICAST_GRANULARITY_MINIMUM));
+    for (auto &d : D) {
+        CUmemAllocationProp ap;
+        std::memset(&ap, 0, sizeof(ap));
+        ap.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+        ap.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        ap.location.id = d.ord;
+        size_t g2 = 0;
+        GP_DRVTRY(g_drv.MemGetAllocationGranularity(&g2, &ap, CU_MEM_ALLOC_GRANULARITY_MINIMUM));
+        gran = std::max(gran, g2);
+    }
+    size = ((payload + NVLS_FLAG_BYTES + gran - 1) / gran) * gran;
+    mp.size = size;
+    const uint64_t flag_off = size - NVLS_FLAG_BYTES;  // last 4 KiB of the allocation, past the payload
+    GP_DRVTRY(g_drv.MulticastCreate(&mc_handle, &mp));
+    mc_created = true;
+    for (auto &d : D) GP_DRVTRY(g_drv.MulticastAddDevice(mc_handle, d.ord));
+    std::vector<CUmemAccessDesc> access(nd);
+    for (int i = 0; i < nd; ++i) {
+        access[i].location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        access[i].location.id = D[i].ord;
+        access[i].flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+    }
+    for (int i = 0; i < nd; ++i) {
+        NvlsDev &d = D[i];
+        GP_TRY(cudaSetDevice(d.ord));
+        CUmemAllocationProp ap;
+        std::memset(&ap, 0, sizeof(ap));
+        ap.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+        ap.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        ap.location.id = d.ord;
+        GP_DRVTRY(g_drv.MemCreate(&d.mem, size, &ap, 0));
+        GP_DRVTRY(g_drv.MemAddressReserve(&d.uc, size, gran, 0, 0));
+        GP_DRVTRY(g_drv.MemMap(d.uc, size, 0, d.mem, 0));
+        d.uc_mapped = true;
+        GP_DRVTRY(g_drv.MemSetAccess(d.uc, size, &access[i], 1));
+        GP_DRVTRY(g_drv.MulticastBindMem(mc_handle, 0, d.mem, 0, size, 0));
+        d.bound = true;
+        GP_TRY(cudaMalloc(&d.bad, sizeof(unsigned long long)));
+        GP_TRY(cudaMalloc(&d.error, sizeof(int)));
+        GP_TRY(cudaMemsetAsync(d.bad, 0, sizeof(unsigned long long), d.st->stream));
+        GP_TRY(cudaMemsetAsync(d.error, 0, sizeof(int), d.st->stream));
+        GP_TRY(cudaMemsetAsync(reinterpret_cast<void *>(d.uc + flag_off), 0, NVLS_FLAG_BYTES, d.st->stream));
+        GP_TRY(cudaEventCreate(&d.ev0));
+        GP_TRY(cudaEventCreate(&d.ev1));
+        int per_sm = 0;
+        GP_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel_fn, NVLS_THREADS, 0));
+        d.grid = d.st->sm_count * std::max(1, std::min(per_sm, ctas_per_sm));
+    }
+    GP_DRVTRY(g_drv.MemAddressReserve(&mc_va, size, gran, 0, 0));
+    GP_DRVTRY(g_drv.MemMap(mc_va, size, 0, mc_handle, 0));
+    mc_mapped = true;
+    GP_DRVTRY(g_drv.MemSetAccess(mc_va, size, access.data(), static_cast<size_t>(nd)));
+    for (auto &d : D) {
+        GP_TRY(cudaSetDevice(d.ord));
+        GP_TRY(cudaStreamSynchronize(d.st->stream));
+    }
+
+    uint32_t barriers_done = 0;
+    auto launch_all = [&](int phases, uint32_t mult, bool timed) -> cudaError_t {
+        for (int r = 0; r < nd; ++r) {
+            NvlsDev &d = D[r];
+            cudaError_t e = cudaSetDevice(d.ord);
+            if (e != cudaSuccess) return e;
+            NvlsArgs a;
+            a.local = reinterpret_cast<uint32_t *>(d.uc);
+            a.mc = reinterpret_cast<uint32_t *>(mc_va);
+            a.flag_local = reinterpret_cast<uint32_t *>(d.uc + flag_off);
+            a.flag_mc = reinterpret_cast<uint32_t *>(mc_va + flag_off);
+            a.mismatches = d.bad;
+            a.error = d.error;
+            a.count = cfg->count;
+            a.seed = cfg->seed;
+            a.mult = mult;
+            a.barrier_base = barriers_done;
+            a.rank = r;
+            a.nranks = nd;
+            a.phases = phases;
+            void *args[] = {&a};
+            if (timed && (e = cudaEventRecord(d.ev0, d.st->stream)) != cudaSuccess) return e;
+            e = cudaLaunchCooperativeKernel(kernel_fn, dim3(d.grid), dim3(NVLS_THREADS),
+                                            args, 0, d.st->stream);
+            if (e != cudaSuccess) return e;
+            if (timed && (e = cudaEventRecord(d.ev1, d.st->stream)) != cudaSuccess) return e;
+        }
+        if (phases & NVLS_REDUCE) barriers_done += 2;
+        return cudaSuccess;
+    };
+    auto sync_all = [&]() -> cudaError_t {
+        for (auto &d : D) {
+            cudaError_t e = cudaSetDevice(d.ord);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(d.st->stream);
+            if (e != cudaSuccess) return e;
+        }
+        return cudaSuccess;
+    };
+
+    // round 1 is the fused launch: fill -> barrier -> reduce+broadcast -> barrier (no verify yet)
+    GP_TRY(launch_all(NVLS_FILL | NVLS_REDUCE, 1, false));
+    GP_TRY(sync_all());
+    int rounds = 1;
+    for (int i = 1; i < cfg->warmup; ++i, ++rounds) {
+        GP_TRY(launch_all(NVLS_REDUCE, 1, false));
+        GP_TRY(sync_all());
+    }
+    std::vector<float> ms;
+    for (int i = 0; i < cfg->iters; ++i, ++rounds) {
+        GP_TRY(launch_all(NVLS_REDUCE, 1, true));
+        GP_TRY(sync_all());
+        float worst = 0;
+        for (auto &d : D) {
+            float m = 0;
+            GP_TRY(cudaEventElapsedTime(&m, d.ev0, d.ev1));
+            worst = std::max(worst, m);
+        }
+        ms.push_back(worst);
+    }
+    // after `rounds` in-place rounds every word is n^(rounds-1) * sum_r x_r[i]  (mod 2^32)
+    uint32_t mult = 1;
+    for (int k = 1; k < rounds; ++k) mult *= static_cast<uint32_t>(nd);
+    GP_TRY(launch_all(NVLS_VERIFY, mult, false));
+    GP_TRY(sync_all());
+    uint64_t bad_total = 0;
+    int timed_out = 0;
+    for (auto &d : D) {
+        GP_TRY(cudaSetDevice(d.ord));
+        unsigned long long h = 0;
+        int e = 0;
+        GP_TRY(cudaMemcpy(&h, d.bad, sizeof(h), cudaMemcpyDeviceToHost));
+        GP_TRY(cudaMemcpy(&e, d.error, sizeof(e), cudaMemcpyDeviceToHost));
+        bad_total += h;
+        timed_out |= e;
+    }
+    out->ndev = nd;
+    out->nccl_version = 0;  // not NCCL
+    out->bytes = payload;
+    out->mismatches = bad_total;
+    out->ms_best = *std::min_element(ms.begin(), ms.end());
+    out->ms_median = median_of(ms);
+    out->algbw_gbps = out->ms_median > 0 ? payload / (out->ms_median * 1e6) : 0;
+    out->busbw_gbps = out->algbw_gbps * 2.0 * (nd - 1) / nd;
+    out->frac_of_peak = out->busbw_gbps / (cfg->peak_gbps > 0 ? cfg->peak_gbps : 900.0);
+    cleanup();
+    if (timed_out) {
+        set_err(err, errlen, "nvls allreduce: a cross-GPU barrier timed out");
+        return GPUPROBE_ECUDA;
+    }
+    if (bad_total) {
+        set_err(err, errlen, "nvls allreduce: %llu elements differ from the expected sum", (unsigned long long)bad_total);
+        return GPUPROBE_FAIL_VERIFY;
+    }
+    return GPUPROBE_OK;
+#undef GP_TRY
+#undef GP_DRVTRY
+}

@@ -118,6 +118,7 @@ SIGNATURES = {
     "gpuprobe_p2p_matrix": (_int, [C.POINTER(P2PCfg), C.POINTER(P2PCell), *_err]),
     "gpuprobe_p2p_expected": (None, [_u64, _u32, _int, _int, C.POINTER(_u64), C.POINTER(_u32)]),
     "gpuprobe_allreduce_i32": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
+    "gpuprobe_allreduce_i32_nvls": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
     "gpuprobe_shutdown": (None, []),
 }
 
@@ -295,6 +296,16 @@ def allreduce_i32(ndev: int, count: int, iters: int = 20, warmup: int = 5, seed:
     cfg = ArCfg(ndev, arr, count, iters, warmup, seed, peak_gbps)
     out, eb = ArResult(), _errbuf()
     _check(lib.gpuprobe_allreduce_i32(C.byref(cfg), C.byref(out), eb, len(eb)), "gpuprobe_allreduce_i32", eb)
+    return out
+
+
+def allreduce_i32_nvls(ndev: int, count: int, iters: int = 20, warmup: int = 5, seed: int = 0, devs=None,
+                       peak_gbps: float = 0.0) -> ArResult:
+    """gpuprobe_allreduce_i32_nvls: the hand-written multimem (NVLS) allreduce kernel."""
+    arr = (C.c_int * ndev)(*devs) if devs is not None else None
+    cfg = ArCfg(ndev, arr, count, iters, warmup, seed, peak_gbps)
+    out, eb = ArResult(), _errbuf()
+    _check(lib.gpuprobe_allreduce_i32_nvls(C.byref(cfg), C.byref(out), eb, len(eb)), "gpuprobe_allreduce_i32_nvls", eb)
     return out
 
 

@@ -251,6 +251,13 @@ GPUPROBE_API void gpuprobe_p2p_expected(uint64_t nwords, uint32_t seed, int src,
  * (ncclCommInitAll); NCCL is loaded at run time (env GPUPROBE_NCCL_LIB, else libnccl.so.2). */
 GPUPROBE_API int gpuprobe_allreduce_i32(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
 
+/* (c') The same check as one hand-written kernel per GPU over NVLink multicast (NVLS): fill,
+ * multimem.ld_reduce (the switch adds) + multimem.st (the switch broadcasts) and verify in a
+ * single cooperative launch, barriers through a multicast flag word.  Same cfg/result as the
+ * NCCL probe (nccl_version is 0).  Returns GPUPROBE_ENOPEER if a device lacks multicast support.
+ * New capability, no reference counterpart. */
+GPUPROBE_API int gpuprobe_allreduce_i32_nvls(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
+
 /* Releases cached per-device state (streams, events, scratch).  Optional. */
 GPUPROBE_API void gpuprobe_shutdown(void);
 

@@ -42,6 +42,17 @@ def main():
         res["allreduce"].append({"ndev": k, "bytes": ar.bytes, "mismatches": ar.mismatches, "ms_median": round(ar.ms_median, 4),
                                  "algbw_gbps": round(ar.algbw_gbps, 1), "busbw_gbps": round(ar.busbw_gbps, 1),
                                  "frac_of_900": round(ar.frac_of_peak, 4), "nccl_version": ar.nccl_version})
+    res["allreduce_nvls_kernel"] = []
+    for k in (2, 4, 8):
+        if k > nd:
+            continue
+        try:
+            ar = gp.allreduce_i32_nvls(k, args.ar_count, iters=20, warmup=5)
+            res["allreduce_nvls_kernel"].append({"ndev": k, "bytes": ar.bytes, "mismatches": ar.mismatches, "ms_median": round(ar.ms_median, 4),
+                                                 "algbw_gbps": round(ar.algbw_gbps, 1), "busbw_gbps": round(ar.busbw_gbps, 1),
+                                                 "frac_of_900": round(ar.frac_of_peak, 4)})
+        except gp.GpuProbeError as e:
+            res["allreduce_nvls_kernel"].append({"ndev": k, "error": str(e)})
     if args.ar_sizes:
         res["allreduce_curve"] = []
         for lg in [int(x) for x in args.ar_sizes.split(",")]:
