@@ -67,6 +67,26 @@ def load_peaks() -> tuple[float, str]:
         return 6650.0, "fallback (B200_PROFILING.md: 6.65 TB/s)"
 
 
+# ----------------------------------------------------------------------------- multi-rank arithmetic
+
+
+def max_over_ranks(x: float, device: str = "cpu") -> float:
+    """The slowest rank's time: every multi-GPU number is the max over ranks (no-op without a process group)."""
+    import torch
+    import torch.distributed as dist
+
+    if not (dist.is_available() and dist.is_initialized()):
+        return float(x)
+    t = torch.tensor([x], device=device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def whole_job_gbps(n_per_rank: int, world: int, steps: int, seconds: float) -> float:
+    """Weak scaling: every rank processed n_per_rank elements per step; value = all ranks' bytes / slowest time."""
+    return BYTES_PER_ELEM * n_per_rank * world * steps / seconds / 1e9
+
+
 # ----------------------------------------------------------------------------- clocks
 
 
@@ -270,11 +290,8 @@ def main() -> int:
         sampler.stop()
         clocks = sampler.summary(t0_wall, t1_wall, clocks_note)
 
-    t = torch.tensor([ms_total], device="cuda", dtype=torch.float64)
-    if distributed:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_max = float(t.item())
-    value = BYTES_PER_ELEM * n * world * args.steps / (ms_max * 1e6)
+    ms_max = max_over_ranks(ms_total, "cuda")
+    value = whole_job_gbps(n, world, args.steps, ms_max / 1e3)
 
     # parity of what was just timed: digest of C against the oracle-checked golden value
     sum64, xor32 = gp.digest_device(d_c, n, dev=dev, stream=stream)
@@ -306,11 +323,8 @@ def main() -> int:
         gp.vectoradd_buffers(h_a, h_b, h_c, n, dev=dev)  # returns after C is back in host memory
     torch.cuda.synchronize()
     te = time.perf_counter() - te0
-    tt = torch.tensor([te], device="cuda", dtype=torch.float64)
-    if distributed:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    e2e_s = float(tt.item())
-    e2e_value = BYTES_PER_ELEM * n * world * e2e_steps / e2e_s / 1e9
+    e2e_s = max_over_ranks(te, "cuda")
+    e2e_value = whole_job_gbps(n, world, e2e_steps, e2e_s)
     # the host-side result is the same C, bit for bit
     hc_u = h_c.view(np.uint32)
     h_sum = int(hc_u.sum(dtype=np.uint64))
