@@ -719,6 +719,48 @@ std::string renderMetrics(const Flags &f, double metricsReadyTs) {
           "1 if the device plugin synchronization barrier on the local is open, 0 otherwise", node, ready(pluginStatusFile));
     gauge(o, "gpu_operator_node_cuda_ready", "1 if cuda synchronization barrier on the local node is open, 0 otherwise", node,
           ready(cudaStatusFile));
+    // The reference samples these with watcher goroutines every 30-60 s (metrics.go:192-301); here they are
+    // evaluated per scrape and cached for the same periods.
+    struct Slow {
+        time_t driverAt = 0, pluginAt = 0, pciAt = 0;
+        double driverOk = 0, driverLastSuccess = 0, devices = -1, pluginLastSuccess = 0, pci = -1;
+    };
+    static Slow slow;
+    const time_t now = time(nullptr);
+    if (now - slow.driverAt >= 60) {  // watchDriverValidation: `nvidia-smi` (chroot'ed in-cluster), metrics.go:237-250
+        slow.driverAt = now;
+        const bool ok = system("nvidia-smi > /dev/null 2>&1") == 0;
+        slow.driverOk = ok ? 1 : 0;
+        if (ok) slow.driverLastSuccess = static_cast<double>(now);
+    }
+    if (now - slow.pluginAt >= 30) {  // watchDevicePluginValidation: countGPUResources, metrics.go:192-235
+        slow.pluginAt = now;
+        ResourceList cap, alloc;
+        if (makeLocalNodeResources()->get(&cap, &alloc).empty()) {
+            slow.devices = static_cast<double>(countGPUResources(cap));
+            if (slow.devices > 0) slow.pluginLastSuccess = static_cast<double>(now);
+        } else {
+            slow.devices = -1;
+        }
+    }
+    if (now - slow.pciAt >= 60) {  // watchNVIDIAPCI: `lspci | grep -i nvidia`, metrics.go:252-301
+        slow.pciAt = now;
+        slow.pci = -1;
+        if (FILE *p = popen("lspci 2>/dev/null | grep -ci nvidia", "r")) {
+            int n = -1;
+            if (fscanf(p, "%d", &n) == 1) slow.pci = n;
+            if (pclose(p) != 0 && slow.pci <= 0) slow.pci = -1;
+        }
+    }
+    gauge(o, "gpu_operator_node_driver_validation", "1 if the driver validation test passed on the local node, 0 otherwise", node,
+          slow.driverOk);
+    gauge(o, "gpu_operator_node_driver_validation_last_success_ts_seconds",
+          "timestamp (in seconds) of the last successful driver test validation", node, slow.driverLastSuccess);
+    gauge(o, "gpu_operator_node_device_plugin_devices_total",
+          "number of GPU devices exposed by the DevicePlugin on the local node. -1 if failing to inspect the node spec.", node, slow.devices);
+    gauge(o, "gpu_operator_node_device_plugin_validation_last_success_ts_seconds",
+          "timestamp (in seconds) of the last time GPU devices were found on the local node spec", node, slow.pluginLastSuccess);
+    gauge(o, "gpu_operator_nvidia_pci_devices_total", "number of NVIDIA devices found in the node. -1 if failing to count", node, slow.pci);
     // new gauges: the probe's achieved bandwidth, written by the workload next to the ready files
     std::ifstream prom(f.outputDir + "/" + probeResultsProm);
     if (prom) {

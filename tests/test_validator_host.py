@@ -271,6 +271,12 @@ def test_metrics_component_serves_reference_gauges_plus_probe_gauges(tmp_path):
         assert 'gpu_operator_node_plugin_ready{node="node-a"} 0' in m
         assert "# TYPE gpu_operator_node_driver_ready gauge" in m
         assert "gpu_operator_node_metrics_ready_ts_seconds" in m
+        # all ten gauges of validator/metrics.go:77-155 are exported, each labelled {node}
+        for name in ["metrics_ready_ts_seconds", "driver_ready", "toolkit_ready", "plugin_ready", "cuda_ready",
+                     "driver_validation", "driver_validation_last_success_ts_seconds", "device_plugin_devices_total",
+                     "device_plugin_validation_last_success_ts_seconds"]:
+            assert f'gpu_operator_node_{name}{{node="node-a"}}' in m, name
+        assert 'gpu_operator_nvidia_pci_devices_total{node="node-a"}' in m
         (out / "cuda-ready").write_text("")
         (out / "host-driver-ready").write_text("")  # metrics.go:169-173: either driver file opens the barrier
         (out / "gpuprobe-results.prom").write_text(

@@ -89,6 +89,25 @@ def test_unaligned_device_pointers_take_the_scalar_path(gp, torch_cuda):
         assert (full[:off_c] == 0).all() and (full[off_c + n:] == 0).all()
 
 
+def test_no_variant_writes_outside_its_output(gp, torch_cuda, variants):
+    """Guard bands around C (compute-sanitizer is closed on this pool, so bounds are checked by sentinel):
+    every variant, sizes that end mid-tile, must leave 4 KiB on both sides of C untouched."""
+    torch = torch_cuda
+    pad = 1024
+    s = torch.cuda.current_stream().cuda_stream
+    for n in [1, 1023, 1025, 4096 + 7, 8192 * 3 + 1, (1 << 20) - 3]:
+        a, b = oc.fill_inputs(n, seed=13, kind=0)
+        want = oc.vectoradd(a, b)
+        da, db = torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()
+        for v in variants:
+            buf = torch.full((n + 2 * pad,), -12345.0, device="cuda", dtype=torch.float32)
+            gp.vectoradd_device(da, db, buf.data_ptr() + 4 * pad, n, variant=v, stream=s)
+            torch.cuda.synchronize()
+            host = buf.cpu().numpy()
+            assert (host[:pad] == -12345.0).all() and (host[pad + n:] == -12345.0).all(), (n, gp.VARIANT_NAMES[v])
+            assert oc.count_mismatch(np.ascontiguousarray(host[pad:pad + n]), want) == 0, (n, gp.VARIANT_NAMES[v])
+
+
 def test_edge_table_exact(gp, torch_cuda, golden):
     torch = torch_cuda
     t = golden["edge_table"]
