@@ -138,7 +138,7 @@ extern "C" int gpuprobe_p2p_matrix(const gpuprobe_p2p_cfg *cfg, gpuprobe_p2p_cel
     }
     const int nd = cfg->ndev;
     if (nd < 2 || nd > MAX_DEVICES || cfg->iters < 1 || cfg->warmup < 0 || cfg->bytes_per_pair == 0 ||
-        (cfg->bytes_per_pair & 15u) || (cfg->mode != GPUPROBE_P2P_SERIAL && cfg->mode != GPUPROBE_P2P_ROUNDS)) {
+        (cfg->bytes_per_pair & 15u) || cfg->mode < GPUPROBE_P2P_SERIAL || cfg->mode > GPUPROBE_P2P_ROUNDS_PUSH) {
         set_err(err, errlen, "bad p2p cfg: ndev=%d bytes=%llu iters=%d warmup=%d mode=%d", nd,
                 (unsigned long long)cfg->bytes_per_pair, cfg->iters, cfg->warmup, cfg->mode);
         return GPUPROBE_EINVAL;
@@ -241,26 +241,32 @@ extern "C" int gpuprobe_p2p_matrix(const gpuprobe_p2p_cfg *cfg, gpuprobe_p2p_cel
         GP_TRY(cudaStreamSynchronize(d.st->stream));
     }
 
-    // One timed launch of src -> dst on dst's stream (events recorded around it).
+    // PULL (default): the kernel runs on dst and loads src's buffer over NVLink. PUSH: it runs on src, loads its own
+    // buffer and stores into dst's landing buffer over NVLink (posted writes need no request packets on the way back).
+    const bool push = cfg->mode == GPUPROBE_P2P_ROUNDS_PUSH;
+    auto runner = [&](int s, int t) { return push ? s : t; };
+    // One timed launch of src -> dst on the running device's stream (events recorded around it).
     auto launch_pair = [&](int s, int t, bool timed) -> cudaError_t {
-        P2PDev &dd = D[t];
+        P2PDev &dd = D[runner(s, t)];
         cudaError_t e = cudaSetDevice(dd.ord);
         if (e != cudaSuccess) return e;
         if (timed && (e = cudaEventRecord(dd.ev0, dd.st->stream)) != cudaSuccess) return e;
         p2p_copy_checksum_kernel<<<p2p_grid(*dd.st, n16), P2P_THREADS, 0, dd.st->stream>>>(
-            reinterpret_cast<const uint4 *>(D[s].src), reinterpret_cast<uint4 *>(dd.dst), n16, dd.scr);
+            reinterpret_cast<const uint4 *>(D[s].src), reinterpret_cast<uint4 *>(D[t].dst), n16, dd.scr);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if (timed) e = cudaEventRecord(dd.ev1, dd.st->stream);
         return e;
     };
     // After the pair's launches: read the kernel's checksum, digest the landed copy, fill the cell.
     auto finish_pair = [&](int s, int t, std::vector<float> &ms) -> int {
+        P2PDev &rr = D[runner(s, t)];
         P2PDev &dd = D[t];
         gpuprobe_p2p_cell &c = cells[s * nd + t];
         P2PScratch head{};
+        GP_CUDA(cudaSetDevice(rr.ord));
+        GP_CUDA(cudaMemcpyAsync(&head, rr.scr, 16, cudaMemcpyDeviceToHost, rr.st->stream));
+        GP_CUDA(cudaStreamSynchronize(rr.st->stream));
         GP_CUDA(cudaSetDevice(dd.ord));
-        GP_CUDA(cudaMemcpyAsync(&head, dd.scr, 16, cudaMemcpyDeviceToHost, dd.st->stream));
-        GP_CUDA(cudaStreamSynchronize(dd.st->stream));
         uint64_t land_sum = 0;
         uint32_t land_xor = 0;
         int r = run_digest(*dd.st, dd.dst, nwords, &land_sum, &land_xor, dd.st->stream, err, errlen);
@@ -300,13 +306,14 @@ extern "C" int gpuprobe_p2p_matrix(const gpuprobe_p2p_cfg *cfg, gpuprobe_p2p_cel
             }
     } else {
         for (int r = 1; r < nd && rc == GPUPROBE_OK; ++r) {
-            // round r: every device reads from the peer r places behind it -> each GPU sends and receives at once
+            // round r: data flows s -> (s + r) mod n for every s at once, so each GPU sends and receives simultaneously
             std::vector<std::vector<float>> ms(nd);
             for (int s = 0; s < nd; ++s) {
                 const int t = (s + r) % nd;
                 if (!cells[s * nd + t].peer_ok) continue;
                 GP_TRY(cudaSetDevice(D[t].ord));
                 GP_TRY(cudaMemsetAsync(D[t].dst, 0, bytes, D[t].st->stream));
+                GP_TRY(cudaStreamSynchronize(D[t].st->stream));  // PUSH writes it from another device's stream
             }
             for (int i = 0; i < cfg->warmup + cfg->iters; ++i) {
                 const bool timed = i >= cfg->warmup;
@@ -317,11 +324,12 @@ extern "C" int gpuprobe_p2p_matrix(const gpuprobe_p2p_cfg *cfg, gpuprobe_p2p_cel
                 for (int s = 0; s < nd; ++s) {
                     const int t = (s + r) % nd;
                     if (!cells[s * nd + t].peer_ok) continue;
-                    GP_TRY(cudaSetDevice(D[t].ord));
-                    GP_TRY(cudaStreamSynchronize(D[t].st->stream));
+                    P2PDev &rr = D[runner(s, t)];
+                    GP_TRY(cudaSetDevice(rr.ord));
+                    GP_TRY(cudaStreamSynchronize(rr.st->stream));
                     if (timed) {
                         float m = 0;
-                        GP_TRY(cudaEventElapsedTime(&m, D[t].ev0, D[t].ev1));
+                        GP_TRY(cudaEventElapsedTime(&m, rr.ev0, rr.ev1));
                         ms[s].push_back(m);
                     }
                 }

@@ -24,7 +24,7 @@ def main():
     gp = ge.load_package().gpuprobe
     nd = args.ndev or gp.device_count()
     res = {"ndev": nd, "bytes_per_pair": args.bytes}
-    for name, mode in (("serial", gp.P2P_SERIAL), ("rounds", gp.P2P_ROUNDS)):
+    for name, mode in (("serial", gp.P2P_SERIAL), ("rounds", gp.P2P_ROUNDS), ("rounds_push", gp.P2P_ROUNDS_PUSH)):
         rc, cells = gp.p2p_matrix(nd, args.bytes, iters=args.iters, warmup=3, mode=mode, raise_on_fail=False)
         g = [cells[s][t].gbps for s in range(nd) for t in range(nd) if s != t]
         res[f"p2p_{name}"] = {
