@@ -380,7 +380,8 @@ def main() -> int:
             for lg in (14, 20, 24, 26, 28, 30, 32):
                 nn = 50_000 if lg == 14 else 1 << lg
                 r = gp.vectoradd(nn, dev=dev, iters=20, warmup=3, verify=1, peak_measured_gbps=peak)
-                sweep.append({"n": nn, "us_median": round(r.ms_median * 1e3, 2), "gbps_median": round(r.gbps_median, 1),
+                sweep.append({"n": nn, "us_median": round(r.ms_median * 1e3, 2), "us_back_to_back": round(r.ms_mean * 1e3, 2),
+                              "gbps_median": round(r.gbps_median, 1),
                               "frac_measured": round(r.frac_measured, 4), "frac_nominal_8000": round(r.frac_nominal, 4),
                               "l2_resident": bool(r.l2_resident)})
             line["sweep"] = sweep

@@ -105,7 +105,8 @@ typedef struct gpuprobe_vadd_result {
     uint32_t variant;    /* variant that ran                              */
     uint64_t mismatches; /* elements where C != regenerated a+b (sanity)  */
     uint64_t algo_bytes; /* 12 * n                                        */
-    double ms_best, ms_median, ms_mean;
+    double ms_best, ms_median; /* per launch, each launch inside its own CUDA-event pair          */
+    double ms_mean;            /* per launch, `iters` launches back to back inside one event pair */
     double gbps_best, gbps_median;
     double frac_nominal, frac_measured; /* of gbps_median */
     int l2_resident;     /* 1 if 12*n fits in L2: not an HBM measurement  */

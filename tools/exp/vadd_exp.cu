@@ -104,6 +104,66 @@ __global__ void __launch_bounds__(T) k_vadd_chunked(const float *__restrict__ a,
     }
 }
 
+// ---- TMA (cp.async.bulk) experiments -----------------------------------------------------------------
+__device__ __forceinline__ uint32_t s32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mb_init(uint64_t *b, uint32_t c) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(s32(b)), "r"(c) : "memory"); }
+__device__ __forceinline__ void mb_expect(uint64_t *b, uint32_t n) { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(s32(b)), "r"(n) : "memory"); }
+__device__ __forceinline__ void mb_wait(uint64_t *b, uint32_t ph) {
+    asm volatile("{\n.reg .pred p;\nW_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@!p bra W_%=;\n}\n" :: "r"(s32(b)), "r"(ph) : "memory");
+}
+__device__ __forceinline__ void g2s(void *sm, const void *g, uint32_t n, uint64_t *b) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" :: "r"(s32(sm)), "l"(g), "r"(n), "r"(s32(b)) : "memory");
+}
+__device__ __forceinline__ void s2g(void *g, const void *sm, uint32_t n) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" :: "l"(g), "r"(s32(sm)), "r"(n) : "memory");
+}
+// pure DMA copy: one thread per CTA moves TILE_B-byte tiles global -> shared -> global through a ring
+template <int TILE_B, int STAGES>
+__global__ void __launch_bounds__(32) k_tma_copy(const float *__restrict__ a, const float *__restrict__, float *__restrict__ c, size_t n_tiles) {
+    extern __shared__ __align__(128) unsigned char sm[];
+    uint64_t *full = (uint64_t *)(sm + (size_t)STAGES * TILE_B);
+    if (threadIdx.x != 0) return;
+    for (int s = 0; s < STAGES; ++s) mb_init(&full[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    const size_t first = blockIdx.x, stride = gridDim.x;
+    const size_t mine = first < n_tiles ? (n_tiles - first + stride - 1) / stride : 0;
+    const char *src = (const char *)a; char *dst = (char *)c;
+    for (size_t k = 0; k < STAGES && k < mine; ++k) { mb_expect(&full[k], TILE_B); g2s(sm + k * TILE_B, src + (first + k * stride) * TILE_B, TILE_B, &full[k]); }
+    for (size_t k = 0; k < mine; ++k) {
+        const int s = k % STAGES;
+        mb_wait(&full[s], (k / STAGES) & 1);
+        s2g(dst + (first + k * stride) * TILE_B, sm + (size_t)s * TILE_B, TILE_B);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        if (k + STAGES < mine) {
+            // the store just issued must have finished READING stage s before it is refilled
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            mb_expect(&full[s], TILE_B);
+            g2s(sm + (size_t)s * TILE_B, src + (first + (k + STAGES) * stride) * TILE_B, TILE_B, &full[s]);
+        }
+    }
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+// vadd: LDG loads (many CTAs in flight), result staged in shared memory, one bulk store per CTA tile
+template <int T, int U>
+__global__ void __launch_bounds__(T) k_vadd_bulkstore(const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ c) {
+    __shared__ __align__(128) float4 tile[T * U];
+    const size_t base = (size_t)blockIdx.x * (T * U * 4) + threadIdx.x * 4;
+    float4 va[U], vb[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) va[u] = ld4<L_NC_NA>(a + base + (size_t)u * T * 4);
+#pragma unroll
+    for (int u = 0; u < U; ++u) vb[u] = ld4<L_NC_NA>(b + base + (size_t)u * T * 4);
+#pragma unroll
+    for (int u = 0; u < U; ++u) tile[u * T + threadIdx.x] = add4(va[u], vb[u]);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        s2g(c + (size_t)blockIdx.x * (T * U * 4), tile, T * U * 16);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    }
+}
+
 struct Exp { std::string name; double bytes_per_elem; std::function<void(const float *, const float *, float *, size_t, cudaStream_t)> run; };
 
 template <int T, int U, int LH, int SH> Exp mk(const char *name) {
@@ -152,6 +212,21 @@ int main(int argc, char **argv) {
     E.push_back(mk<256, 2, L_NC_NA, S_WT>("vadd_stwt"));
     E.push_back(mk<256, 2, L_NC_NA, S_CG>("vadd_stcg"));
     E.push_back(mk<256, 2, L_CS, S_CS>("vadd_ldcs_stcs"));
+    E.push_back({"vadd_bulkstore_t256_u1", 12, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd_bulkstore<256, 1><<<(unsigned)(n / (256 * 1 * 4)), 256, 0, s>>>(a, b, c); }});
+    E.push_back({"vadd_bulkstore_t256_u2", 12, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd_bulkstore<256, 2><<<(unsigned)(n / (256 * 2 * 4)), 256, 0, s>>>(a, b, c); }});
+    E.push_back({"vadd_bulkstore_t512_u2", 12, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd_bulkstore<512, 2><<<(unsigned)(n / (512 * 2 * 4)), 512, 0, s>>>(a, b, c); }});
+    {
+        auto add_tma = [&](const char *name, auto kern, int tile_b, int stages, int ctas) {
+            size_t smem = (size_t)stages * tile_b + stages * 8;
+            CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            E.push_back({name, 8, [=](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { kern<<<sms * ctas, 32, smem, s>>>(a, b, c, n * 4 / tile_b); }});
+        };
+        add_tma("tmacopy_16k_s8_x1", k_tma_copy<16384, 8>, 16384, 8, 1);
+        add_tma("tmacopy_16k_s4_x3", k_tma_copy<16384, 4>, 16384, 4, 3);
+        add_tma("tmacopy_32k_s6_x1", k_tma_copy<32768, 6>, 32768, 6, 1);
+        add_tma("tmacopy_8k_s8_x3", k_tma_copy<8192, 8>, 8192, 8, 3);
+        add_tma("tmacopy_4k_s8_x6", k_tma_copy<4096, 8>, 4096, 8, 6);
+    }
     for (int k : {1, 2, 4, 8, 16})
         E.push_back({"chunked_x" + std::to_string(k), 12, [k, sms](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd_chunked<256, 2><<<sms * k, 256, 0, s>>>(a, b, c, n / 2048); }});
 
