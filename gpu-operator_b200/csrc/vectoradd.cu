@@ -123,6 +123,19 @@ vadd_scalar_kernel(const float *__restrict__ a, const float *__restrict__ b, flo
         c[i] = __fadd_rn(__ldg(a + i), __ldg(b + i));
 }
 
+// Launch-latency-bound sizes (the sample's 50,000 elements): ONE launch, 128-bit accesses with a per-thread
+// bounds check, the last < 4 elements by scalar accesses in the same kernel. Needs 16-byte aligned pointers.
+__global__ void __launch_bounds__(VADD_THREADS)
+vadd_small_kernel(const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ c, uint32_t n) {
+    const uint32_t i = (blockIdx.x * VADD_THREADS + threadIdx.x) * 4u;
+    if (i + 3u < n) {
+        const Vec<4> x = vload<4, false>(a + i), y = vload<4, false>(b + i);
+        vstore<4, false>(c + i, vadd<4>(x, y));
+    } else {
+        for (uint32_t j = i; j < n; ++j) c[j] = __fadd_rn(__ldg(a + j), __ldg(b + j));
+    }
+}
+
 // ------------------------------------------------------------------ TMA (cp.async.bulk) ring
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
@@ -387,6 +400,7 @@ verify_kernel(const float *__restrict__ c, uint64_t first, uint64_t n, uint32_t 
 
 // Measured best on B200 at every HBM-resident size (profiles/r01_vadd_variants.md): the smallest tile.
 constexpr int DEFAULT_VARIANT = GPUPROBE_VADD_LDG128_U1;
+constexpr uint64_t SMALL_N_LIMIT = 1ull << 22;  // below this a launch costs more than the data movement
 
 struct VariantInfo {
     int vec_floats;  // alignment requirement in floats (0: none)
@@ -434,11 +448,23 @@ static int scalar_grid(const DeviceState &st, uint64_t n) {
 int launch_vadd(DeviceState &st, const float *a, const float *b, float *c, uint64_t n, int variant,
                 cudaStream_t stream, char *err, size_t errlen) {
     if (n == 0) return 0;
-    if (variant == GPUPROBE_VADD_AUTO) variant = DEFAULT_VARIANT;
     if (variant < 0 || variant >= GPUPROBE_VADD_NUM_VARIANTS) {
         set_err(err, errlen, "unknown vectorAdd variant %d", variant);
         return GPUPROBE_EINVAL;
     }
+    const bool aligned16 = ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) |
+                             reinterpret_cast<uintptr_t>(c)) & 15u) == 0;
+    if (variant == GPUPROBE_VADD_SMALL || (variant == GPUPROBE_VADD_AUTO && n < SMALL_N_LIMIT && n % 1024u != 0)) {
+        // a ragged launch-bound size would otherwise cost two launches (tiles + tail)
+        if (aligned16 && n < (1ull << 31)) {
+            const unsigned grid = static_cast<unsigned>((n + VADD_THREADS * 4 - 1) / (VADD_THREADS * 4));
+            vadd_small_kernel<<<grid, VADD_THREADS, 0, stream>>>(a, b, c, static_cast<uint32_t>(n));
+            GP_CUDA(cudaGetLastError());
+            return 1;
+        }
+        if (variant == GPUPROBE_VADD_SMALL) variant = GPUPROBE_VADD_SCALAR;
+    }
+    if (variant == GPUPROBE_VADD_AUTO) variant = DEFAULT_VARIANT;
     VariantInfo vi = variant_info(variant);
     const uintptr_t align_mask = vi.vec_floats ? static_cast<uintptr_t>(vi.vec_floats) * 4u - 1u : 0u;
     const bool aligned = ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) |
@@ -669,7 +695,9 @@ extern "C" int gpuprobe_vectoradd(const gpuprobe_vadd_cfg *cfg, gpuprobe_vadd_re
     const uint64_t n = cfg->n_elems;
     out->n = n;
     out->algo_bytes = 12ull * n;
-    out->variant = static_cast<uint32_t>(cfg->variant == GPUPROBE_VADD_AUTO ? DEFAULT_VARIANT : cfg->variant);
+    out->variant = static_cast<uint32_t>(cfg->variant != GPUPROBE_VADD_AUTO           ? cfg->variant
+                                         : (cfg->n_elems < SMALL_N_LIMIT && cfg->n_elems % 1024u) ? GPUPROBE_VADD_SMALL
+                                                                                                  : DEFAULT_VARIANT);
     out->l2_resident = (12ull * n <= st.l2_bytes) ? 1 : 0;
     if (n == 0) return GPUPROBE_OK;  // empty input: nothing to add, trivially correct
 

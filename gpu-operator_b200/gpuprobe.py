@@ -30,10 +30,11 @@ VADD_LDG128_U2, VADD_LDG128_U4, VADD_LDG128_U8 = 1, 2, 3
 VADD_LDG256_U2, VADD_LDG256_U4 = 4, 5
 VADD_TMA, VADD_PERSIST128, VADD_SCALAR, VADD_TMA_8K, VADD_LDG256_U2_EF = 6, 7, 8, 9, 10
 VADD_LDG128_U1, VADD_LDG256_U1 = 11, 12
-VADD_NUM_VARIANTS = 13
+VADD_SMALL = 13
+VADD_NUM_VARIANTS = 14
 VARIANT_NAMES = {
     0: "auto", 1: "ldg128_u2", 2: "ldg128_u4", 3: "ldg128_u8", 4: "ldg256_u2", 5: "ldg256_u4",
-    6: "tma_16k", 7: "persist128", 8: "scalar", 9: "tma_8k", 10: "ldg256_u2_ef", 11: "ldg128_u1", 12: "ldg256_u1",
+    6: "tma_16k", 7: "persist128", 8: "scalar", 9: "tma_8k", 10: "ldg256_u2_ef", 11: "ldg128_u1", 12: "ldg256_u1", 13: "small",
 }
 
 P2P_SERIAL, P2P_ROUNDS, P2P_ROUNDS_PUSH = 0, 1, 2

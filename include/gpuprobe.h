@@ -72,7 +72,8 @@ extern "C" {
 #define GPUPROBE_VADD_LDG256_U2_EF 10 /* 256-bit ld/st with L2::evict_first on loads and stores    */
 #define GPUPROBE_VADD_LDG128_U1 11 /* 128-bit ld/st, 1 vector of each input per thread: 4 KiB tiles  */
 #define GPUPROBE_VADD_LDG256_U1 12 /* 256-bit ld/st, 1 vector of each input per thread: 8 KiB tiles  */
-#define GPUPROBE_VADD_NUM_VARIANTS 13
+#define GPUPROBE_VADD_SMALL 13 /* one launch, bounds-checked 128-bit ld/st: AUTO's choice for ragged n < 2^22 */
+#define GPUPROBE_VADD_NUM_VARIANTS 14
 
 typedef struct gpuprobe_devinfo {
     char name[128];
