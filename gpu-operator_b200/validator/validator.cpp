@@ -568,6 +568,8 @@ static std::string runWorkload(Runtime &rt, const char *specPath, const char *wh
             const char *eq = strchr(*ev, '=');
             if (eq) pod.initEnv[std::string(*ev, eq - *ev)] = eq + 1;
         }
+    // the plugin workload (one allocated GPU) must not overwrite the cuda workload's node-wide results
+    if (!resourceName.empty()) pod.initEnv["GPUPROBE_RESULTS_BASENAME"] = "gpuprobe-plugin-results";
     std::string name;
     e = rt.launcher->create(pod, &name);
     if (!e.empty()) return sprintfStr("failed to create %s validation pod %s, err %s", what, pod.generateName.c_str(), e.c_str());

@@ -171,7 +171,8 @@ int main(void) {
     struct stat st;
     if (stat(outDir, &st) == 0 && S_ISDIR(st.st_mode)) {
         for (int k = 0; k < 2; ++k) {
-            std::string path = std::string(outDir) + (k ? "/gpuprobe-results.prom" : "/gpuprobe-results.json");
+            const char *base = getenv("GPUPROBE_RESULTS_BASENAME");  // set for the plugin workload (one GPU)
+            std::string path = std::string(outDir) + "/" + (base && *base ? base : "gpuprobe-results") + (k ? ".prom" : ".json");
             std::string tmp = path + ".tmp";
             if (FILE *fp = fopen(tmp.c_str(), "w")) {
                 const std::string body = k ? prom.str() : json.str();
