@@ -20,11 +20,15 @@ def main():
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--out", default="")
     ap.add_argument("--ar-sizes", default="", help="extra allreduce counts (log2 list) for a latency curve at max ndev")
+    ap.add_argument("--modes", default="serial,rounds,rounds_push")
+    ap.add_argument("--no-allreduce", action="store_true")
     args = ap.parse_args()
     gp = ge.load_package().gpuprobe
     nd = args.ndev or gp.device_count()
     res = {"ndev": nd, "bytes_per_pair": args.bytes}
     for name, mode in (("serial", gp.P2P_SERIAL), ("rounds", gp.P2P_ROUNDS), ("rounds_push", gp.P2P_ROUNDS_PUSH)):
+        if name not in args.modes.split(","):
+            continue
         rc, cells = gp.p2p_matrix(nd, args.bytes, iters=args.iters, warmup=3, mode=mode, raise_on_fail=False)
         g = [cells[s][t].gbps for s in range(nd) for t in range(nd) if s != t]
         res[f"p2p_{name}"] = {
@@ -36,7 +40,7 @@ def main():
         }
     res["allreduce"] = []
     for k in (2, 4, 8):
-        if k > nd:
+        if k > nd or args.no_allreduce:
             continue
         ar = gp.allreduce_i32(k, args.ar_count, iters=20, warmup=5)
         res["allreduce"].append({"ndev": k, "bytes": ar.bytes, "mismatches": ar.mismatches, "ms_median": round(ar.ms_median, 4),
@@ -44,7 +48,7 @@ def main():
                                  "frac_of_900": round(ar.frac_of_peak, 4), "nccl_version": ar.nccl_version})
     res["allreduce_nvls_kernel"] = []
     for k in (2, 4, 8):
-        if k > nd:
+        if k > nd or args.no_allreduce:
             continue
         try:
             ar = gp.allreduce_i32_nvls(k, args.ar_count, iters=20, warmup=5)
