@@ -22,6 +22,7 @@
 #include <ctime>
 #include <sstream>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/gpuprobe.h"
@@ -85,20 +86,35 @@ int main(void) {
         std::ostringstream frac;
         frac << "# HELP gpu_operator_node_cuda_hbm_roofline_fraction achieved vectorAdd bandwidth as a fraction of 8000 GB/s\n"
              << "# TYPE gpu_operator_node_cuda_hbm_roofline_fraction gauge\n";
+        // every GPU at once, one host thread each (the library serialises per device, not across devices):
+        // all HBM stacks of the node are loaded together, and the pass takes the time of one probe, not of ndev
+        std::vector<gpuprobe_vadd_result> results(ndev);
+        std::vector<int> rcs(ndev, GPUPROBE_OK);
+        std::vector<std::string> errs(ndev);
+        {
+            std::vector<std::thread> workers;
+            for (int d = 0; d < ndev; ++d)
+                workers.emplace_back([&, d]() {
+                    gpuprobe_vadd_cfg cfg{};
+                    cfg.dev = d;
+                    cfg.n_elems = vaddElems;
+                    cfg.iters = 20;
+                    cfg.warmup = 3;
+                    cfg.verify = 3;
+                    char e[512] = "";
+                    rcs[d] = gpuprobe_vectoradd(&cfg, &results[d], e, sizeof(e));
+                    errs[d] = e;
+                });
+            for (auto &w : workers) w.join();
+        }
         for (int d = 0; d < ndev; ++d) {
-            gpuprobe_vadd_cfg cfg{};
-            cfg.dev = d;
-            cfg.n_elems = vaddElems;
-            cfg.iters = 20;
-            cfg.warmup = 3;
-            cfg.verify = 3;
-            gpuprobe_vadd_result r{};
-            rc = gpuprobe_vectoradd(&cfg, &r, err, sizeof(err));
+            const gpuprobe_vadd_result &r = results[d];
+            rc = rcs[d];
             const bool slow = rc == GPUPROBE_OK && minHbm > 0 && r.frac_nominal < minHbm && !r.l2_resident;
             if (rc != GPUPROBE_OK || slow) {
                 ++failed;
                 fprintf(stderr, "vectorAdd bandwidth probe on GPU %d failed: %s %s\n", d,
-                        slow ? gpuprobe_strerror(GPUPROBE_FAIL_BANDWIDTH) : gpuprobe_strerror(rc), err);
+                        slow ? gpuprobe_strerror(GPUPROBE_FAIL_BANDWIDTH) : gpuprobe_strerror(rc), errs[d].c_str());
             }
             printf("GPU %d: vectorAdd n=%llu  %.1f GB/s (%.3f of 8000 GB/s nominal), %llu mismatches\n", d,
                    (unsigned long long)r.n, r.gbps_median, r.frac_nominal, (unsigned long long)r.mismatches);
@@ -151,7 +167,21 @@ int main(void) {
         cfg.iters = 20;
         cfg.warmup = 5;
         gpuprobe_ar_result r{};
-        rc = gpuprobe_allreduce_i32(&cfg, &r, err, sizeof(err));
+        // GPUPROBE_AR_IMPL: "nccl" (default; validates the library path), "nvls" (the hand-written multimem kernel:
+        // no communicator set-up, higher bus bandwidth), "both" (NCCL result reported, both must verify)
+        const char *impl = getenv("GPUPROBE_AR_IMPL") ? getenv("GPUPROBE_AR_IMPL") : "nccl";
+        if (!strcmp(impl, "nvls")) {
+            rc = gpuprobe_allreduce_i32_nvls(&cfg, &r, err, sizeof(err));
+        } else {
+            rc = gpuprobe_allreduce_i32(&cfg, &r, err, sizeof(err));
+            if (rc == GPUPROBE_OK && !strcmp(impl, "both")) {
+                gpuprobe_ar_result r2{};
+                rc = gpuprobe_allreduce_i32_nvls(&cfg, &r2, err, sizeof(err));
+                printf("allreduce int32 x%d (NVLS kernel): busbw %.1f GB/s, %llu mismatches\n", r2.ndev, r2.busbw_gbps,
+                       (unsigned long long)r2.mismatches);
+                json << ",\"allreduce_nvls\":{\"rc\":" << rc << ",\"busbw_gbps\":" << r2.busbw_gbps << ",\"mismatches\":" << r2.mismatches << "}";
+            }
+        }
         const bool slow = rc == GPUPROBE_OK && minLink > 0 && r.frac_of_peak < minLink;
         if (rc != GPUPROBE_OK || slow) {
             ++failed;
