@@ -33,6 +33,8 @@ constexpr int NVLS_THREADS = 512;
 constexpr uint64_t NVLS_FLAG_BYTES = 4096;  // the flag word lives in its own page-slice behind the payload
 constexpr unsigned long long NVLS_SPIN_TIMEOUT_NS = 4000000000ull;
 
+constexpr int NVLS_MAX_PEERS = 16;
+
 enum : int { NVLS_FILL = 1, NVLS_REDUCE = 2, NVLS_VERIFY = 4 };
 
 struct NvlsArgs {
@@ -47,6 +49,8 @@ struct NvlsArgs {
     uint32_t mult;          // verify: expected = mult * sum_r x_r[i]
     uint32_t barrier_base;  // number of barriers completed before this launch
     int rank, nranks, phases;
+    int algo;               // 0: NVLS multimem; 1: two-shot over peer mappings (pull-reduce my slice, push it to everyone)
+    uint32_t *peer[NVLS_MAX_PEERS];  // algo 1: unicast mapping of every rank's buffer (peer[rank] == local)
 };
 
 __device__ __forceinline__ uint32_t mm_ld_reduce_add_u32(const uint32_t *mc) {
@@ -61,6 +65,48 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     return t;
+}
+
+__device__ __forceinline__ uint4 ld_cg128(const uint32_t *p) {  // L2-coherent load (peer data changes between rounds)
+    uint4 r;
+    asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+    return r;
+}
+__device__ __forceinline__ void st_128(uint32_t *p, const uint4 &v) {
+    asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// Two-shot allreduce of words [lo, hi) over peer mappings: load the slice from every rank (NR-1 loads cross NVLink),
+// add, store the sum into every rank's buffer (NR-1 stores cross NVLink). NR is a compile-time rank count so that all
+// peer loads of a vector are in flight together.
+template <int NR>
+__device__ __forceinline__ void p2p_reduce_broadcast(const NvlsArgs &a, uint64_t lo, uint64_t hi, uint64_t gtid, uint64_t gstride) {
+    const uint64_t lo4 = lo / 4, hi4 = hi / 4;  // lo is a multiple of 32 words
+    for (uint64_t v = lo4 + gtid; v < hi4; v += gstride) {
+        uint4 x[NR];
+#pragma unroll
+        for (int r = 0; r < NR; ++r) x[r] = ld_cg128(a.peer[r] + v * 4);
+        uint4 acc = x[0];
+#pragma unroll
+        for (int r = 1; r < NR; ++r) {
+            acc.x += x[r].x;
+            acc.y += x[r].y;
+            acc.z += x[r].z;
+            acc.w += x[r].w;
+        }
+#pragma unroll
+        for (int r = 0; r < NR; ++r) st_128(a.peer[r] + v * 4, acc);
+    }
+    // < 4 trailing words of the whole buffer; max(): an empty slice clamped to `count` must not redo its neighbour's tail
+    for (uint64_t i = max(hi4 * 4, lo) + gtid; i < hi; i += gstride) {
+        uint32_t acc = 0;
+        for (int r = 0; r < NR; ++r) {
+            uint32_t w;
+            asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(w) : "l"(a.peer[r] + i) : "memory");
+            acc += w;
+        }
+        for (int r = 0; r < NR; ++r) a.peer[r][i] = acc;
+    }
 }
 
 // All CTAs of all ranks meet here. Local arrival is the cooperative grid barrier; one thread then adds 1 to the
@@ -111,6 +157,16 @@ __global__ void __launch_bounds__(NVLS_THREADS) nvls_allreduce_kernel(NvlsArgs a
         uint64_t per = (a.count + a.nranks - 1) / a.nranks;
         per = (per + 31) & ~31ull;
         const uint64_t lo = min(per * a.rank, a.count), hi = min(lo + per, a.count);
+        if (a.algo == 1) {
+            switch (a.nranks) {
+            case 2: p2p_reduce_broadcast<2>(a, lo, hi, gtid, gstride); break;
+            case 4: p2p_reduce_broadcast<4>(a, lo, hi, gtid, gstride); break;
+            case 8: p2p_reduce_broadcast<8>(a, lo, hi, gtid, gstride); break;
+            default: break;  // rejected on the host
+            }
+            cross_gpu_barrier(grid, a, bar++);
+            goto reduce_done;
+        }
         constexpr uint64_t TILE = static_cast<uint64_t>(NVLS_THREADS) * NVLS_UNROLL;
         const uint64_t n_tiles = (hi - lo) / TILE;
         for (uint64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
@@ -124,6 +180,7 @@ __global__ void __launch_bounds__(NVLS_THREADS) nvls_allreduce_kernel(NvlsArgs a
         for (uint64_t i = lo + n_tiles * TILE + gtid; i < hi; i += gstride) mm_st_u32(a.mc + i, mm_ld_reduce_add_u32(a.mc + i));
         cross_gpu_barrier(grid, a, bar++);  // every slice has been broadcast
     }
+reduce_done:
 
     if (a.phases & NVLS_VERIFY) {
         unsigned long long bad = 0;
@@ -216,7 +273,7 @@ struct NvlsDev {
 
 using namespace gp;
 
-extern "C" int gpuprobe_allreduce_i32_nvls(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen) {
+static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, int algo, char *err, size_t errlen) {
     if (!cfg || !out) {
         set_err(err, errlen, "null cfg/out");
         return GPUPROBE_EINVAL;
@@ -226,6 +283,10 @@ extern "C" int gpuprobe_allreduce_i32_nvls(const gpuprobe_ar_cfg *cfg, gpuprobe_
     if (nd < 2 || nd > MAX_DEVICES || cfg->count == 0 || cfg->iters < 1 || cfg->warmup < 0) {
         set_err(err, errlen, "bad allreduce cfg: ndev=%d count=%llu iters=%d warmup=%d", nd,
                 (unsigned long long)cfg->count, cfg->iters, cfg->warmup);
+        return GPUPROBE_EINVAL;
+    }
+    if (algo == 1 && nd != 2 && nd != 4 && nd != 8) {
+        set_err(err, errlen, "the peer two-shot allreduce is built for 2, 4 or 8 ranks (got %d)", nd);
         return GPUPROBE_EINVAL;
     }
     std::vector<NvlsDev> D(nd);
@@ -354,7 +415,8 @@ extern "C" int gpuprobe_allreduce_i32_nvls(const gpuprobe_ar_cfg *cfg, gpuprobe_
         GP_DRVTRY(g_drv.MemAddressReserve(&d.uc, size, gran, 0, 0));
         GP_DRVTRY(g_drv.MemMap(d.uc, size, 0, d.mem, 0));
         d.uc_mapped = true;
-        GP_DRVTRY(g_drv.MemSetAccess(d.uc, size, &access[i], 1));
+        // every rank may read and write every rank's buffer (the two-shot algorithm; harmless for NVLS)
+        GP_DRVTRY(g_drv.MemSetAccess(d.uc, size, access.data(), static_cast<size_t>(nd)));
         GP_DRVTRY(g_drv.MulticastBindMem(mc_handle, 0, d.mem, 0, size, 0));
         d.bound = true;
         GP_TRY(cudaMalloc(&d.bad, sizeof(unsigned long long)));
@@ -397,6 +459,8 @@ extern "C" int gpuprobe_allreduce_i32_nvls(const gpuprobe_ar_cfg *cfg, gpuprobe_
             a.rank = r;
             a.nranks = nd;
             a.phases = phases;
+            a.algo = algo;
+            for (int q = 0; q < NVLS_MAX_PEERS; ++q) a.peer[q] = q < nd ? reinterpret_cast<uint32_t *>(D[q].uc) : nullptr;
             void *args[] = {&a};
             if (timed && (e = cudaEventRecord(d.ev0, d.st->stream)) != cudaSuccess) return e;
             e = cudaLaunchCooperativeKernel(kernel_fn, dim3(d.grid), dim3(NVLS_THREADS),
@@ -473,4 +537,12 @@ extern "C" int gpuprobe_allreduce_i32_nvls(const gpuprobe_ar_cfg *cfg, gpuprobe_
     return GPUPROBE_OK;
 #undef GP_TRY
 #undef GP_DRVTRY
+}
+
+extern "C" int gpuprobe_allreduce_i32_nvls(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen) {
+    return allreduce_symmetric(cfg, out, 0, err, errlen);
+}
+
+extern "C" int gpuprobe_allreduce_i32_p2p(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen) {
+    return allreduce_symmetric(cfg, out, 1, err, errlen);
 }

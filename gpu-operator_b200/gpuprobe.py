@@ -120,6 +120,7 @@ SIGNATURES = {
     "gpuprobe_p2p_expected": (None, [_u64, _u32, _int, _int, C.POINTER(_u64), C.POINTER(_u32)]),
     "gpuprobe_allreduce_i32": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
     "gpuprobe_allreduce_i32_nvls": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
+    "gpuprobe_allreduce_i32_p2p": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
     "gpuprobe_shutdown": (None, []),
 }
 
@@ -307,6 +308,16 @@ def allreduce_i32_nvls(ndev: int, count: int, iters: int = 20, warmup: int = 5, 
     cfg = ArCfg(ndev, arr, count, iters, warmup, seed, peak_gbps)
     out, eb = ArResult(), _errbuf()
     _check(lib.gpuprobe_allreduce_i32_nvls(C.byref(cfg), C.byref(out), eb, len(eb)), "gpuprobe_allreduce_i32_nvls", eb)
+    return out
+
+
+def allreduce_i32_p2p(ndev: int, count: int, iters: int = 20, warmup: int = 5, seed: int = 0, devs=None,
+                      peak_gbps: float = 0.0) -> ArResult:
+    """gpuprobe_allreduce_i32_p2p: two-shot allreduce over peer mappings (2, 4 or 8 ranks)."""
+    arr = (C.c_int * ndev)(*devs) if devs is not None else None
+    cfg = ArCfg(ndev, arr, count, iters, warmup, seed, peak_gbps)
+    out, eb = ArResult(), _errbuf()
+    _check(lib.gpuprobe_allreduce_i32_p2p(C.byref(cfg), C.byref(out), eb, len(eb)), "gpuprobe_allreduce_i32_p2p", eb)
     return out
 
 

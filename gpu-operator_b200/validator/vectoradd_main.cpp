@@ -168,10 +168,13 @@ int main(void) {
         cfg.warmup = 5;
         gpuprobe_ar_result r{};
         // GPUPROBE_AR_IMPL: "nccl" (default; validates the library path), "nvls" (the hand-written multimem kernel:
-        // no communicator set-up, higher bus bandwidth), "both" (NCCL result reported, both must verify)
+        // no communicator set-up, higher bus bandwidth), "p2p" (two-shot kernel over peer mappings, 2/4/8 GPUs),
+        // "both" (NCCL result reported, NCCL and NVLS must both verify)
         const char *impl = getenv("GPUPROBE_AR_IMPL") ? getenv("GPUPROBE_AR_IMPL") : "nccl";
         if (!strcmp(impl, "nvls")) {
             rc = gpuprobe_allreduce_i32_nvls(&cfg, &r, err, sizeof(err));
+        } else if (!strcmp(impl, "p2p")) {
+            rc = gpuprobe_allreduce_i32_p2p(&cfg, &r, err, sizeof(err));
         } else {
             rc = gpuprobe_allreduce_i32(&cfg, &r, err, sizeof(err));
             if (rc == GPUPROBE_OK && !strcmp(impl, "both")) {

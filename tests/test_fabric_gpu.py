@@ -67,3 +67,14 @@ def test_nvls_and_nccl_agree_on_bandwidth_order_of_magnitude(gp, ndev):
     b = gp.allreduce_i32(nd, 1 << 26, iters=5, warmup=2)
     assert a.mismatches == 0 and b.mismatches == 0
     assert a.busbw_gbps > 0.3 * b.busbw_gbps
+
+
+@pytest.mark.parametrize("count", [1, 5, 1000, 4096 * 3 + 5, (16 << 20) + 7])
+def test_p2p_two_shot_allreduce_kernel_bit_exact(gp, ndev, count):
+    """Same buffers and barriers as the NVLS kernel, data over plain peer mappings."""
+    for nd in [n for n in (2, 4, 8) if n <= ndev]:
+        res = gp.allreduce_i32_p2p(nd, count, iters=3, warmup=2, seed=6)
+        assert res.mismatches == 0 and res.ndev == nd and res.bytes == 4 * count
+    with pytest.raises(gp.GpuProbeError) as e:
+        gp.allreduce_i32_p2p(3, 1024) if ndev >= 3 else gp.allreduce_i32_p2p(1, 1024)
+    assert e.value.code == gp.EINVAL

@@ -25,6 +25,11 @@ for nd in ndevs:
             row["nvls"] = {"us": round(a.ms_median * 1e3, 1), "busbw": round(a.busbw_gbps, 1), "algbw": round(a.algbw_gbps, 1), "mism": a.mismatches}
         except gp.GpuProbeError as e:
             row["nvls"] = {"error": str(e)}
+        try:
+            c = gp.allreduce_i32_p2p(nd, 1 << lg, iters=20, warmup=5)
+            row["p2p2shot"] = {"us": round(c.ms_median * 1e3, 1), "busbw": round(c.busbw_gbps, 1), "mism": c.mismatches}
+        except gp.GpuProbeError as e:
+            row["p2p2shot"] = {"error": str(e)}
         if not args.skip_nccl:
             b = gp.allreduce_i32(nd, 1 << lg, iters=20, warmup=5)
             row["nccl"] = {"us": round(b.ms_median * 1e3, 1), "busbw": round(b.busbw_gbps, 1), "mism": b.mismatches}
