@@ -49,7 +49,10 @@ struct NvlsArgs {
     uint32_t mult;          // verify: expected = mult * sum_r x_r[i]
     uint32_t barrier_base;  // number of barriers completed before this launch
     int rank, nranks, phases;
-    int algo;               // 0: NVLS multimem; 1: two-shot over peer mappings (pull-reduce my slice, push it to everyone)
+    int algo;               // 0: NVLS multimem; 1: two-shot over peer mappings (pull-reduce my slice, push it to everyone);
+                            // 2: hybrid (head of the slice by NVLS, tail by peer mappings, on disjoint CTAs)
+    int hybrid_permille;    // algo 2: share of the slice that goes through the switch, in 1/1000
+    int hybrid_nvls_blocks; // algo 2: CTAs [0, this) run the NVLS part, the rest the peer part
     uint32_t *peer[NVLS_MAX_PEERS];  // algo 1: unicast mapping of every rank's buffer (peer[rank] == local)
 };
 
@@ -157,30 +160,46 @@ __global__ void __launch_bounds__(NVLS_THREADS) nvls_allreduce_kernel(NvlsArgs a
         uint64_t per = (a.count + a.nranks - 1) / a.nranks;
         per = (per + 31) & ~31ull;
         const uint64_t lo = min(per * a.rank, a.count), hi = min(lo + per, a.count);
-        if (a.algo == 1) {
+        auto p2p_part = [&](uint64_t from, uint64_t to, uint64_t tid0, uint64_t stride0) {
             switch (a.nranks) {
-            case 2: p2p_reduce_broadcast<2>(a, lo, hi, gtid, gstride); break;
-            case 4: p2p_reduce_broadcast<4>(a, lo, hi, gtid, gstride); break;
-            case 8: p2p_reduce_broadcast<8>(a, lo, hi, gtid, gstride); break;
+            case 2: p2p_reduce_broadcast<2>(a, from, to, tid0, stride0); break;
+            case 4: p2p_reduce_broadcast<4>(a, from, to, tid0, stride0); break;
+            case 8: p2p_reduce_broadcast<8>(a, from, to, tid0, stride0); break;
             default: break;  // rejected on the host
             }
-            cross_gpu_barrier(grid, a, bar++);
-            goto reduce_done;
-        }
-        constexpr uint64_t TILE = static_cast<uint64_t>(NVLS_THREADS) * NVLS_UNROLL;
-        const uint64_t n_tiles = (hi - lo) / TILE;
-        for (uint64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-            const uint64_t base = lo + t * TILE + threadIdx.x;
-            uint32_t v[NVLS_UNROLL];
+        };
+        // words [from, to) through the switch: CTA `bid` of `nb` CTAs
+        auto nvls_part = [&](uint64_t from, uint64_t to, uint64_t bid, uint64_t nb) {
+            constexpr uint64_t TILE = static_cast<uint64_t>(NVLS_THREADS) * NVLS_UNROLL;
+            const uint64_t n_tiles = (to - from) / TILE;
+            for (uint64_t t = bid; t < n_tiles; t += nb) {
+                const uint64_t base = from + t * TILE + threadIdx.x;
+                uint32_t v[NVLS_UNROLL];
 #pragma unroll
-            for (int u = 0; u < NVLS_UNROLL; ++u) v[u] = mm_ld_reduce_add_u32(a.mc + base + u * NVLS_THREADS);
+                for (int u = 0; u < NVLS_UNROLL; ++u) v[u] = mm_ld_reduce_add_u32(a.mc + base + u * NVLS_THREADS);
 #pragma unroll
-            for (int u = 0; u < NVLS_UNROLL; ++u) mm_st_u32(a.mc + base + u * NVLS_THREADS, v[u]);
+                for (int u = 0; u < NVLS_UNROLL; ++u) mm_st_u32(a.mc + base + u * NVLS_THREADS, v[u]);
+            }
+            for (uint64_t i = from + n_tiles * TILE + bid * NVLS_THREADS + threadIdx.x; i < to; i += nb * NVLS_THREADS)
+                mm_st_u32(a.mc + i, mm_ld_reduce_add_u32(a.mc + i));
+        };
+        if (a.algo == 1) {
+            p2p_part(lo, hi, gtid, gstride);
+        } else if (a.algo == 2 && a.hybrid_nvls_blocks > 0 && a.hybrid_nvls_blocks < static_cast<int>(gridDim.x)) {
+            // hybrid: the head of the slice goes through the switch, the tail over peer mappings, on disjoint CTAs,
+            // so the switch's reduction engine and the spare link bandwidth work at the same time
+            const uint64_t nb = static_cast<uint64_t>(a.hybrid_nvls_blocks);
+            const uint64_t head = ((hi - lo) / 1000u * static_cast<uint64_t>(a.hybrid_permille)) & ~static_cast<uint64_t>(31);
+            const uint64_t mid = (lo + head < hi) ? lo + head : hi;
+            if (blockIdx.x < nb)
+                nvls_part(lo, mid, blockIdx.x, nb);
+            else
+                p2p_part(mid, hi, (blockIdx.x - nb) * NVLS_THREADS + threadIdx.x, (gridDim.x - nb) * NVLS_THREADS);
+        } else {
+            nvls_part(lo, hi, blockIdx.x, gridDim.x);
         }
-        for (uint64_t i = lo + n_tiles * TILE + gtid; i < hi; i += gstride) mm_st_u32(a.mc + i, mm_ld_reduce_add_u32(a.mc + i));
         cross_gpu_barrier(grid, a, bar++);  // every slice has been broadcast
     }
-reduce_done:
 
     if (a.phases & NVLS_VERIFY) {
         unsigned long long bad = 0;
@@ -285,7 +304,7 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
                 (unsigned long long)cfg->count, cfg->iters, cfg->warmup);
         return GPUPROBE_EINVAL;
     }
-    if (algo == 1 && nd != 2 && nd != 4 && nd != 8) {
+    if (algo >= 1 && nd != 2 && nd != 4 && nd != 8) {
         set_err(err, errlen, "the peer two-shot allreduce is built for 2, 4 or 8 ranks (got %d)", nd);
         return GPUPROBE_EINVAL;
     }
@@ -320,6 +339,9 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
     int unroll = 8, ctas_per_sm = 2;
     if (const char *u = getenv("GPUPROBE_NVLS_UNROLL")) unroll = atoi(u);
     if (const char *c = getenv("GPUPROBE_NVLS_CTAS")) ctas_per_sm = std::max(1, atoi(c));
+    int hybrid_permille = 800, hybrid_block_permille = 500;
+    if (const char *h = getenv("GPUPROBE_HYBRID_PERMILLE")) hybrid_permille = std::max(0, std::min(1000, atoi(h)));
+    if (const char *h = getenv("GPUPROBE_HYBRID_BLOCK_PERMILLE")) hybrid_block_permille = std::max(1, std::min(999, atoi(h)));
     const void *kernel_fn = unroll >= 16  ? reinterpret_cast<const void *>(nvls_allreduce_kernel<16>)
                             : unroll >= 8 ? reinterpret_cast<const void *>(nvls_allreduce_kernel<8>)
                             : unroll >= 4 ? reinterpret_cast<const void *>(nvls_allreduce_kernel<4>)
@@ -460,6 +482,8 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
             a.nranks = nd;
             a.phases = phases;
             a.algo = algo;
+            a.hybrid_permille = hybrid_permille;
+            a.hybrid_nvls_blocks = std::max(1, std::min(d.grid - 1, d.grid * hybrid_block_permille / 1000));
             for (int q = 0; q < NVLS_MAX_PEERS; ++q) a.peer[q] = q < nd ? reinterpret_cast<uint32_t *>(D[q].uc) : nullptr;
             void *args[] = {&a};
             if (timed && (e = cudaEventRecord(d.ev0, d.st->stream)) != cudaSuccess) return e;
@@ -541,6 +565,10 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
 
 extern "C" int gpuprobe_allreduce_i32_nvls(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen) {
     return allreduce_symmetric(cfg, out, 0, err, errlen);
+}
+
+extern "C" int gpuprobe_allreduce_i32_hybrid(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen) {
+    return allreduce_symmetric(cfg, out, 2, err, errlen);
 }
 
 extern "C" int gpuprobe_allreduce_i32_p2p(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen) {

@@ -121,6 +121,7 @@ SIGNATURES = {
     "gpuprobe_allreduce_i32": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
     "gpuprobe_allreduce_i32_nvls": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
     "gpuprobe_allreduce_i32_p2p": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
+    "gpuprobe_allreduce_i32_hybrid": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
     "gpuprobe_shutdown": (None, []),
 }
 
@@ -318,6 +319,16 @@ def allreduce_i32_p2p(ndev: int, count: int, iters: int = 20, warmup: int = 5, s
     cfg = ArCfg(ndev, arr, count, iters, warmup, seed, peak_gbps)
     out, eb = ArResult(), _errbuf()
     _check(lib.gpuprobe_allreduce_i32_p2p(C.byref(cfg), C.byref(out), eb, len(eb)), "gpuprobe_allreduce_i32_p2p", eb)
+    return out
+
+
+def allreduce_i32_hybrid(ndev: int, count: int, iters: int = 20, warmup: int = 5, seed: int = 0, devs=None,
+                         peak_gbps: float = 0.0) -> ArResult:
+    """gpuprobe_allreduce_i32_hybrid: NVLS for the head of each slice, peer mappings for the tail."""
+    arr = (C.c_int * ndev)(*devs) if devs is not None else None
+    cfg = ArCfg(ndev, arr, count, iters, warmup, seed, peak_gbps)
+    out, eb = ArResult(), _errbuf()
+    _check(lib.gpuprobe_allreduce_i32_hybrid(C.byref(cfg), C.byref(out), eb, len(eb)), "gpuprobe_allreduce_i32_hybrid", eb)
     return out
 
 

@@ -78,3 +78,11 @@ def test_p2p_two_shot_allreduce_kernel_bit_exact(gp, ndev, count):
     with pytest.raises(gp.GpuProbeError) as e:
         gp.allreduce_i32_p2p(3, 1024) if ndev >= 3 else gp.allreduce_i32_p2p(1, 1024)
     assert e.value.code == gp.EINVAL
+
+
+@pytest.mark.parametrize("count", [1, 5, 1000, 4096 * 3 + 5, (16 << 20) + 7])
+def test_hybrid_allreduce_kernel_bit_exact(gp, ndev, count):
+    """NVLS head + peer-mapping tail on disjoint CTAs of one kernel."""
+    for nd in [n for n in (2, 4, 8) if n <= ndev]:
+        res = gp.allreduce_i32_hybrid(nd, count, iters=3, warmup=2, seed=8)
+        assert res.mismatches == 0 and res.ndev == nd and res.bytes == 4 * count

@@ -30,6 +30,11 @@ for nd in ndevs:
             row["p2p2shot"] = {"us": round(c.ms_median * 1e3, 1), "busbw": round(c.busbw_gbps, 1), "mism": c.mismatches}
         except gp.GpuProbeError as e:
             row["p2p2shot"] = {"error": str(e)}
+        try:
+            h = gp.allreduce_i32_hybrid(nd, 1 << lg, iters=20, warmup=5)
+            row["hybrid"] = {"us": round(h.ms_median * 1e3, 1), "busbw": round(h.busbw_gbps, 1), "mism": h.mismatches}
+        except gp.GpuProbeError as e:
+            row["hybrid"] = {"error": str(e)}
         if not args.skip_nccl:
             b = gp.allreduce_i32(nd, 1 << lg, iters=20, warmup=5)
             row["nccl"] = {"us": round(b.ms_median * 1e3, 1), "busbw": round(b.busbw_gbps, 1), "mism": b.mismatches}
