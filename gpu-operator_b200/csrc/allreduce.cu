@@ -34,12 +34,15 @@ static std::mutex g_nccl_mu;
 static int load_nccl(char *err, size_t errlen) {
     std::lock_guard<std::mutex> lock(g_nccl_mu);
     if (g_nccl.handle) return GPUPROBE_OK;
-    const char *cands[3] = {getenv("GPUPROBE_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+    // Order: an explicit path; a copy some other component of this process already loaded (two different NCCLs
+    // in one process break whichever is bound second); the system library.
     void *h = nullptr;
-    for (const char *c : cands) {
-        if (!c || !*c) continue;
-        h = dlopen(c, RTLD_NOW | RTLD_LOCAL);
+    const char *explicit_path = getenv("GPUPROBE_NCCL_LIB");
+    if (explicit_path && *explicit_path) h = dlopen(explicit_path, RTLD_NOW | RTLD_LOCAL);
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL | RTLD_NOLOAD);
+    for (const char *c : {"libnccl.so.2", "libnccl.so"}) {
         if (h) break;
+        h = dlopen(c, RTLD_NOW | RTLD_LOCAL);
     }
     if (!h) {
         set_err(err, errlen, "cannot load NCCL (set GPUPROBE_NCCL_LIB): %s", dlerror());
