@@ -790,8 +790,9 @@ extern "C" int gpuprobe_vectoradd(const gpuprobe_vadd_cfg *cfg, gpuprobe_vadd_re
 // ---------------------------------------------------------------- host buffers (the e2e path)
 
 namespace gp {
-constexpr uint64_t BUF_CHUNK_ELEMS = 8ull << 20;  // 32 MiB per array per chunk
-constexpr int BUF_SLOTS = 3;
+constexpr uint64_t BUF_CHUNK_ELEMS = 8ull << 20;  // default: 32 MiB per array per chunk
+constexpr int BUF_SLOTS = 3;                      // default number of chunks in flight
+constexpr int BUF_MAX_SLOTS = 4;                  // = number of copy streams per device
 
 struct BufSlot {
     float *d_a = nullptr, *d_b = nullptr, *d_c = nullptr;
@@ -824,11 +825,16 @@ extern "C" int gpuprobe_vectoradd_buffers(int dev, const float *a, const float *
     std::lock_guard<std::mutex> lock(st.mu);
 
     const bool direct = is_pinned(a) && is_pinned(b) && is_pinned(c);
-    const uint64_t chunk = std::min<uint64_t>(n, BUF_CHUNK_ELEMS);
-    const int slots = static_cast<int>(std::min<uint64_t>(BUF_SLOTS, (n + chunk - 1) / chunk));
-    BufSlot slot[BUF_SLOTS];
+    // tuning knobs for experiments; the defaults are the measured best (profiles/r01_e2e_chunks.md)
+    uint64_t chunk_elems = BUF_CHUNK_ELEMS;
+    int max_slots = BUF_SLOTS;
+    if (const char *e = getenv("GPUPROBE_BUF_CHUNK_LOG2")) chunk_elems = 1ull << std::max(10, std::min(30, atoi(e)));
+    if (const char *e = getenv("GPUPROBE_BUF_SLOTS")) max_slots = std::max(1, std::min(BUF_MAX_SLOTS, atoi(e)));
+    const uint64_t chunk = std::min<uint64_t>(n, chunk_elems);
+    const int slots = static_cast<int>(std::min<uint64_t>(static_cast<uint64_t>(max_slots), (n + chunk - 1) / chunk));
+    BufSlot slot[BUF_MAX_SLOTS];
     auto cleanup = [&]() {
-        for (int s = 0; s < BUF_SLOTS; ++s) {
+        for (int s = 0; s < BUF_MAX_SLOTS; ++s) {
             cudaFree(slot[s].d_a);
             cudaFree(slot[s].d_b);
             cudaFree(slot[s].d_c);
