@@ -809,6 +809,16 @@ static bool is_pinned(const void *p) {
     }
     return at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged;
 }
+
+// The address the device can use for a pinned host pointer (UVA), or null if the memory is not mapped.
+static const void *device_alias(const void *p) {
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return nullptr;
+    }
+    return at.type == cudaMemoryTypeHost ? at.devicePointer : nullptr;
+}
 }  // namespace gp
 
 extern "C" int gpuprobe_vectoradd_buffers(int dev, const float *a, const float *b, float *c, uint64_t n, char *err,
@@ -825,6 +835,21 @@ extern "C" int gpuprobe_vectoradd_buffers(int dev, const float *a, const float *
     std::lock_guard<std::mutex> lock(st.mu);
 
     const bool direct = is_pinned(a) && is_pinned(b) && is_pinned(c);
+    // Pinned, device-mapped buffers: no staging at all. The add kernel loads A and B straight from host memory over
+    // PCIe and stores C back over PCIe, so both directions of the link run for the whole call and nothing is
+    // allocated on the device. Measured at the link limit for every kernel variant (profiles/r01_e2e_chunks.md).
+    // GPUPROBE_BUF_ZEROCOPY=0 forces the staged pipeline below (comparison runs).
+    const char *zc = getenv("GPUPROBE_BUF_ZEROCOPY");
+    if (direct && !(zc && *zc == '0')) {
+        const float *da = static_cast<const float *>(device_alias(a)), *db = static_cast<const float *>(device_alias(b));
+        float *dc = static_cast<float *>(const_cast<void *>(device_alias(c)));
+        if (da && db && dc) {
+            rc = launch_vadd(st, da, db, dc, n, GPUPROBE_VADD_AUTO, st.stream, err, errlen);
+            if (rc < 0) return rc;
+            GP_CUDA(cudaStreamSynchronize(st.stream));
+            return GPUPROBE_OK;
+        }
+    }
     // tuning knobs for experiments; the defaults are the measured best (profiles/r01_e2e_chunks.md)
     uint64_t chunk_elems = BUF_CHUNK_ELEMS;
     int max_slots = BUF_SLOTS;

@@ -181,9 +181,11 @@ GPUPROBE_API int gpuprobe_vectoradd(const gpuprobe_vadd_cfg *cfg, gpuprobe_vadd_
 
 /* Caller-supplied HOST inputs: copies a,b to the device (chunked, pipelined over separate
  * copy streams), adds, copies C back, so the CALLER's host loop does the bit-exact compare
- * -- the sample's h_A/h_B -> cudaMemcpy -> kernel -> cudaMemcpy -> h_C sequence.  Pinned
- * buffers (gpuprobe_host_alloc) are copied directly; pageable ones go through the
- * library's pinned bounce buffers. */
+ * -- the sample's h_A/h_B -> cudaMemcpy -> kernel -> cudaMemcpy -> h_C sequence.  Pinned,
+ * device-mapped buffers (gpuprobe_host_alloc) are not staged at all: the add kernel loads A
+ * and B from host memory over PCIe and stores C back over PCIe (env GPUPROBE_BUF_ZEROCOPY=0
+ * forces the staged pipeline); pageable ones go through the library's pinned bounce buffers
+ * and the chunked H2D / kernel / D2H pipeline. */
 GPUPROBE_API int gpuprobe_vectoradd_buffers(int dev, const float *a, const float *b, float *c, uint64_t n, char *err,
                                size_t errlen);
 
