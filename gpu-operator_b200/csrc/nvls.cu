@@ -339,7 +339,7 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
     int unroll = 8, ctas_per_sm = 2;
     if (const char *u = getenv("GPUPROBE_NVLS_UNROLL")) unroll = atoi(u);
     if (const char *c = getenv("GPUPROBE_NVLS_CTAS")) ctas_per_sm = std::max(1, atoi(c));
-    int hybrid_permille = 900, hybrid_block_permille = 400;  // measured best at 8 ranks (profiles/r01_fabric.md)
+    int hybrid_permille = 950, hybrid_block_permille = 350;  // centre of the measured plateau at 8 ranks (profiles/r01_fabric.md)
     if (const char *h = getenv("GPUPROBE_HYBRID_PERMILLE")) hybrid_permille = std::max(0, std::min(1000, atoi(h)));
     if (const char *h = getenv("GPUPROBE_HYBRID_BLOCK_PERMILLE")) hybrid_block_permille = std::max(1, std::min(999, atoi(h)));
     const void *kernel_fn = unroll >= 16  ? reinterpret_cast<const void *>(nvls_allreduce_kernel<16>)

@@ -272,8 +272,8 @@ GPUPROBE_API int gpuprobe_allreduce_i32_p2p(const gpuprobe_ar_cfg *cfg, gpuprobe
 /* (c''') Hybrid of the two: the head of each rank's slice goes through the switch (multimem), the
  * tail over peer mappings, on disjoint CTAs of the same kernel, so the switch's reduction engine and
  * the link bandwidth it leaves idle are used together.  ndev must be 2, 4 or 8.  The split is set by
- * env GPUPROBE_HYBRID_PERMILLE (share of the data through the switch, default 900) and
- * GPUPROBE_HYBRID_BLOCK_PERMILLE (share of the CTAs on that part, default 400). */
+ * env GPUPROBE_HYBRID_PERMILLE (share of the data through the switch, default 950) and
+ * GPUPROBE_HYBRID_BLOCK_PERMILLE (share of the CTAs on that part, default 350). */
 GPUPROBE_API int gpuprobe_allreduce_i32_hybrid(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
 
 /* Releases cached per-device state (streams, events, scratch).  Optional. */
