@@ -551,11 +551,12 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
     out->frac_of_peak = out->busbw_gbps / (cfg->peak_gbps > 0 ? cfg->peak_gbps : 900.0);
     cleanup();
     if (timed_out) {
-        set_err(err, errlen, "nvls allreduce: a cross-GPU barrier timed out");
+        set_err(err, errlen, "allreduce kernel (%s): a cross-GPU barrier timed out", algo == 0 ? "nvls" : algo == 1 ? "two-shot" : "hybrid");
         return GPUPROBE_ECUDA;
     }
     if (bad_total) {
-        set_err(err, errlen, "nvls allreduce: %llu elements differ from the expected sum", (unsigned long long)bad_total);
+        set_err(err, errlen, "allreduce kernel (%s): %llu elements differ from the expected sum",
+                algo == 0 ? "nvls" : algo == 1 ? "two-shot" : "hybrid", (unsigned long long)bad_total);
         return GPUPROBE_FAIL_VERIFY;
     }
     return GPUPROBE_OK;
