@@ -175,8 +175,14 @@ def cpu_host_loop_gbps(steps: int, warmup: int, sample_log2: int, min_seconds: f
     total = sum(times)
     gbps = BYTES_PER_ELEM * n * len(times) / total / 1e9
     check = oc.digest(c[: 1 << 20]) == oc.vectoradd_digest(1 << 20, 0, oc.GEN_UNIT)
+    # the same loop on ONE thread (SURVEY.md section 8d asks for both), three passes
+    t1 = []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        oc.vectoradd_into(a, b, c, 1)
+        t1.append(time.perf_counter() - t0)
     return {"gbps": gbps, "ms_per_step": 1e3 * total / len(times), "steps": len(times), "threads": threads,
-            "n": n, "verified": bool(check)}
+            "n": n, "verified": bool(check), "gbps_1thread": BYTES_PER_ELEM * n / min(t1) / 1e9}
 
 
 def run_reference(args, rank: int) -> int:
@@ -191,7 +197,7 @@ def run_reference(args, rank: int) -> int:
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args.gpus),
         "cpu_baseline": {"value": round(r["gbps"], 2), "unit": UNIT, "cores": r["threads"], "kind": "port",
-                         "sample": sample, "verified": r["verified"]},
+                         "sample": sample, "verified": r["verified"], "value_1thread": round(r["gbps_1thread"], 2)},
         "e2e": {"value": round(r["gbps"], 2), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
         "note": "the reference's arithmetic for this path is a prebuilt third-party binary + Go host code, neither "
@@ -365,7 +371,7 @@ def main() -> int:
             "value": round(r["gbps"], 2), "unit": UNIT, "cores": r["threads"], "kind": "port",
             "sample": f"{r['steps']} passes of the host loop over the first 2^{CPU_SAMPLE_LOG2} of the workload's "
                       f"2^{LOG2_N} elements (~{r['steps'] * r['ms_per_step'] / 1e3:.0f} s of CPU work)",
-            "verified": r["verified"]}
+            "verified": r["verified"], "value_1thread": round(r["gbps_1thread"], 2)}
         from oracle import oracle as oc
 
         line["parity"]["oracle_digest_first_2p28_equal"] = (
