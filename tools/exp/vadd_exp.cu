@@ -63,6 +63,26 @@ __global__ void __launch_bounds__(T) k_vadd8(const float *__restrict__ a, const 
         asm volatile("st.global.L1::no_allocate.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" :: "l"(c + base + (size_t)u * T * 8), "f"(r[0]), "f"(r[1]), "f"(r[2]), "f"(r[3]), "f"(r[4]), "f"(r[5]), "f"(r[6]), "f"(r[7]) : "memory");
     }
 }
+// 256-bit with explicit L2 eviction priorities: LP/SP in {0: none, 1: evict_first, 2: evict_last, 3: evict_normal}
+#define LD8(HINT) asm volatile("ld.global.nc.L1::no_allocate" HINT ".v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]) : "l"(p))
+#define ST8(HINT) asm volatile("st.global.L1::no_allocate" HINT ".v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" :: "l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory")
+template <int LP> __device__ __forceinline__ void ld8p(float *v, const float *p) {
+    if constexpr (LP == 1) LD8(".L2::evict_first"); else if constexpr (LP == 2) LD8(".L2::evict_last"); else if constexpr (LP == 3) LD8(".L2::evict_normal"); else LD8("");
+}
+template <int SP> __device__ __forceinline__ void st8p(float *p, const float *v) {
+    if constexpr (SP == 1) ST8(".L2::evict_first"); else if constexpr (SP == 2) ST8(".L2::evict_last"); else if constexpr (SP == 3) ST8(".L2::evict_normal"); else ST8("");
+}
+template <int T, int LP, int SP>
+__global__ void __launch_bounds__(T) k_vadd8_pol(const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ c) {
+    const size_t base = (size_t)blockIdx.x * (T * 8) + threadIdx.x * 8;
+    float x[8], y[8], r[8];
+    ld8p<LP>(x, a + base);
+    ld8p<LP>(y, b + base);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r[i] = __fadd_rn(x[i], y[i]);
+    st8p<SP>(c + base, r);
+}
+
 // read-only (2 streams), write-only, copy
 template <int T, int U>
 __global__ void __launch_bounds__(T) k_read2(const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ c) {
@@ -212,6 +232,15 @@ int main(int argc, char **argv) {
     E.push_back(mk<256, 2, L_NC_NA, S_WT>("vadd_stwt"));
     E.push_back(mk<256, 2, L_NC_NA, S_CG>("vadd_stcg"));
     E.push_back(mk<256, 2, L_CS, S_CS>("vadd_ldcs_stcs"));
+#define POL(LP, SP, NAME) E.push_back({NAME, 12, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd8_pol<128, LP, SP><<<(unsigned)(n / (128 * 8)), 128, 0, s>>>(a, b, c); }})
+    POL(0, 0, "pol_ld-none_st-none");
+    POL(1, 0, "pol_ld-first_st-none");
+    POL(1, 2, "pol_ld-first_st-last");
+    POL(0, 2, "pol_ld-none_st-last");
+    POL(1, 1, "pol_ld-first_st-first");
+    POL(2, 1, "pol_ld-last_st-first");
+    POL(3, 3, "pol_ld-normal_st-normal");
+    POL(0, 1, "pol_ld-none_st-first");
     E.push_back({"vadd_bulkstore_t256_u1", 12, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd_bulkstore<256, 1><<<(unsigned)(n / (256 * 1 * 4)), 256, 0, s>>>(a, b, c); }});
     E.push_back({"vadd_bulkstore_t256_u2", 12, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd_bulkstore<256, 2><<<(unsigned)(n / (256 * 2 * 4)), 256, 0, s>>>(a, b, c); }});
     E.push_back({"vadd_bulkstore_t512_u2", 12, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd_bulkstore<512, 2><<<(unsigned)(n / (512 * 2 * 4)), 512, 0, s>>>(a, b, c); }});
