@@ -34,6 +34,20 @@ static std::mutex g_nccl_mu;
 static int load_nccl(char *err, size_t errlen) {
     std::lock_guard<std::mutex> lock(g_nccl_mu);
     if (g_nccl.handle) return GPUPROBE_OK;
+#if defined(GPUPROBE_NCCL_STATIC)
+    // `make NCCL_STATIC=1`: libnccl_static.a is linked in (the validator image ships no CUDA user libraries).
+    (void)err;
+    (void)errlen;
+    g_nccl.GetVersion = &ncclGetVersion;
+    g_nccl.CommInitAll = &ncclCommInitAll;
+    g_nccl.CommDestroy = &ncclCommDestroy;
+    g_nccl.AllReduce = &ncclAllReduce;
+    g_nccl.GroupStart = &ncclGroupStart;
+    g_nccl.GroupEnd = &ncclGroupEnd;
+    g_nccl.GetErrorString = &ncclGetErrorString;
+    g_nccl.handle = &g_nccl;
+    return GPUPROBE_OK;
+#endif
     // Order: an explicit path; a copy some other component of this process already loaded (two different NCCLs
     // in one process break whichever is bound second); the system library.
     void *h = nullptr;
