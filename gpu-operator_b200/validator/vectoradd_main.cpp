@@ -175,6 +175,13 @@ int main(void) {
             rc = gpuprobe_allreduce_i32_nvls(&cfg, &r, err, sizeof(err));
         } else if (!strcmp(impl, "p2p")) {
             rc = gpuprobe_allreduce_i32_p2p(&cfg, &r, err, sizeof(err));
+        } else if (!strcmp(impl, "hybrid")) {
+            rc = gpuprobe_allreduce_i32_hybrid(&cfg, &r, err, sizeof(err));
+        } else if (!strcmp(impl, "kernel")) {
+            // the fastest hand-written kernel for this rank count (profiles/r01_fabric.md)
+            rc = ndev == 2                          ? gpuprobe_allreduce_i32_p2p(&cfg, &r, err, sizeof(err))
+                 : (ndev == 4 || ndev == 8)         ? gpuprobe_allreduce_i32_hybrid(&cfg, &r, err, sizeof(err))
+                                                    : gpuprobe_allreduce_i32_nvls(&cfg, &r, err, sizeof(err));
         } else {
             rc = gpuprobe_allreduce_i32(&cfg, &r, err, sizeof(err));
             if (rc == GPUPROBE_OK && !strcmp(impl, "both")) {
