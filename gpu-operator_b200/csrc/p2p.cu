@@ -138,7 +138,7 @@ extern "C" int gpuprobe_p2p_matrix(const gpuprobe_p2p_cfg *cfg, gpuprobe_p2p_cel
     }
     const int nd = cfg->ndev;
     if (nd < 2 || nd > MAX_DEVICES || cfg->iters < 1 || cfg->warmup < 0 || cfg->bytes_per_pair == 0 ||
-        (cfg->bytes_per_pair & 15u) || cfg->mode < GPUPROBE_P2P_SERIAL || cfg->mode > GPUPROBE_P2P_ROUNDS_PUSH) {
+        (cfg->bytes_per_pair & 15u) || cfg->mode < GPUPROBE_P2P_SERIAL || cfg->mode > GPUPROBE_P2P_SERIAL_PUSH) {
         set_err(err, errlen, "bad p2p cfg: ndev=%d bytes=%llu iters=%d warmup=%d mode=%d", nd,
                 (unsigned long long)cfg->bytes_per_pair, cfg->iters, cfg->warmup, cfg->mode);
         return GPUPROBE_EINVAL;
@@ -243,7 +243,8 @@ extern "C" int gpuprobe_p2p_matrix(const gpuprobe_p2p_cfg *cfg, gpuprobe_p2p_cel
 
     // PULL (default): the kernel runs on dst and loads src's buffer over NVLink. PUSH: it runs on src, loads its own
     // buffer and stores into dst's landing buffer over NVLink (posted writes need no request packets on the way back).
-    const bool push = cfg->mode == GPUPROBE_P2P_ROUNDS_PUSH;
+    const bool push = cfg->mode == GPUPROBE_P2P_ROUNDS_PUSH || cfg->mode == GPUPROBE_P2P_SERIAL_PUSH;
+    const bool serial = cfg->mode == GPUPROBE_P2P_SERIAL || cfg->mode == GPUPROBE_P2P_SERIAL_PUSH;
     auto runner = [&](int s, int t) { return push ? s : t; };
     // One timed launch of src -> dst on the running device's stream (events recorded around it).
     auto launch_pair = [&](int s, int t, bool timed) -> cudaError_t {
@@ -287,19 +288,21 @@ extern "C" int gpuprobe_p2p_matrix(const gpuprobe_p2p_cfg *cfg, gpuprobe_p2p_cel
         return GPUPROBE_OK;
     };
 
-    if (cfg->mode == GPUPROBE_P2P_SERIAL) {
+    if (serial) {
         for (int s = 0; s < nd && rc == GPUPROBE_OK; ++s)
             for (int t = 0; t < nd; ++t) {
                 if (s == t || !cells[s * nd + t].peer_ok) continue;
                 P2PDev &dd = D[t];
+                P2PDev &rr = D[runner(s, t)];
                 GP_TRY(cudaSetDevice(dd.ord));
                 GP_TRY(cudaMemsetAsync(dd.dst, 0, bytes, dd.st->stream));
+                GP_TRY(cudaStreamSynchronize(dd.st->stream));  // PUSH writes it from the source's stream
                 for (int i = 0; i < cfg->warmup; ++i) GP_TRY(launch_pair(s, t, false));
                 std::vector<float> ms(cfg->iters);
                 for (int i = 0; i < cfg->iters; ++i) {
                     GP_TRY(launch_pair(s, t, true));
-                    GP_TRY(cudaEventSynchronize(dd.ev1));
-                    GP_TRY(cudaEventElapsedTime(&ms[i], dd.ev0, dd.ev1));
+                    GP_TRY(cudaEventSynchronize(rr.ev1));
+                    GP_TRY(cudaEventElapsedTime(&ms[i], rr.ev0, rr.ev1));
                 }
                 rc = finish_pair(s, t, ms);
                 if (rc) break;

@@ -37,7 +37,7 @@ VARIANT_NAMES = {
     6: "tma_16k", 7: "persist128", 8: "scalar", 9: "tma_8k", 10: "ldg256_u2_ef", 11: "ldg128_u1", 12: "ldg256_u1", 13: "small",
 }
 
-P2P_SERIAL, P2P_ROUNDS, P2P_ROUNDS_PUSH = 0, 1, 2
+P2P_SERIAL, P2P_ROUNDS, P2P_ROUNDS_PUSH, P2P_SERIAL_PUSH = 0, 1, 2, 3
 
 
 class DevInfo(C.Structure):

@@ -117,6 +117,7 @@ typedef struct gpuprobe_vadd_result {
 #define GPUPROBE_P2P_SERIAL 0 /* one directed pair at a time                                  */
 #define GPUPROBE_P2P_ROUNDS 1 /* ndev-1 rounds, dst = (src + r) mod ndev, all pairs of a round concurrently */
 #define GPUPROBE_P2P_ROUNDS_PUSH 2 /* same schedule, but the kernel runs on src and STORES into dst over NVLink */
+#define GPUPROBE_P2P_SERIAL_PUSH 3 /* one directed pair at a time, kernel on src storing into dst               */
 
 typedef struct gpuprobe_p2p_cfg {
     int ndev;

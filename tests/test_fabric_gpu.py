@@ -15,7 +15,7 @@ def ndev(gp):
     return n
 
 
-@pytest.mark.parametrize("mode", [0, 1, 2])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3])
 def test_p2p_matrix_checksums_match_oracle(gp, ndev, mode):
     nd = min(ndev, 8)
     nbytes = (64 << 20) + 16 * 7  # ragged: not a multiple of the kernel's tile
