@@ -398,7 +398,7 @@ verify_kernel(const float *__restrict__ c, uint64_t first, uint64_t n, uint32_t 
 
 // ------------------------------------------------------------------ host: dispatch
 
-// Measured best on B200 at every HBM-resident size (profiles/r01_vadd_variants.md): the smallest tile.
+// Measured best on B200 at every HBM-resident size (profiles/r01_vadd_ncu_full.md, sections 3-6): the smallest tile.
 constexpr int DEFAULT_VARIANT = GPUPROBE_VADD_LDG128_U1;
 constexpr uint64_t SMALL_N_LIMIT = 1ull << 22;  // below this a launch costs more than the data movement
 
