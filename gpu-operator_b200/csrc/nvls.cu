@@ -53,6 +53,7 @@ struct NvlsArgs {
                             // 2: hybrid (head of the slice by NVLS, tail by peer mappings, on disjoint CTAs)
     int hybrid_permille;    // algo 2: share of the slice that goes through the switch, in 1/1000
     int hybrid_nvls_blocks; // algo 2: CTAs [0, this) run the NVLS part, the rest the peer part
+    int barrier_peer;       // 1: no multicast on this box -- barrier through per-rank flag slots written with peer stores
     uint32_t *peer[NVLS_MAX_PEERS];  // algo 1: unicast mapping of every rank's buffer (peer[rank] == local)
 };
 
@@ -117,7 +118,7 @@ __device__ __forceinline__ void p2p_reduce_broadcast(const NvlsArgs &a, uint64_t
 // before is visible to whoever acquires the flag) and waits until its own copy shows that all ranks did the same.
 __device__ void cross_gpu_barrier(cg::grid_group &grid, const NvlsArgs &a, uint32_t index) {
     grid.sync();
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
+    if (blockIdx.x == 0 && threadIdx.x == 0 && !a.barrier_peer) {
         __threadfence_system();
         asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" ::"l"(a.flag_mc), "r"(1u) : "memory");
         const uint32_t target = (a.barrier_base + index + 1u) * static_cast<uint32_t>(a.nranks);
@@ -126,6 +127,27 @@ __device__ void cross_gpu_barrier(cg::grid_group &grid, const NvlsArgs &a, uint3
             uint32_t seen;
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.flag_local) : "memory");
             if (static_cast<int32_t>(seen - target) >= 0) break;
+            if (globaltimer_ns() - t0 > NVLS_SPIN_TIMEOUT_NS) {
+                *a.error = 1;
+                break;
+            }
+            __nanosleep(200);
+        }
+        __threadfence_system();
+    }
+    if (blockIdx.x == 0 && threadIdx.x < a.nranks && a.barrier_peer) {
+        // No multicast: thread r publishes this rank's epoch into slot [rank] of rank r's flag page with a peer
+        // store, then waits until rank r's epoch shows up in slot [r] of the local page.
+        const uint64_t flag_off = static_cast<uint64_t>(a.flag_local - a.local);
+        const uint32_t epoch = a.barrier_base + index + 1u;
+        const int r = threadIdx.x;
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.peer[r] + flag_off + 64 + a.rank), "r"(epoch) : "memory");
+        const unsigned long long t0 = globaltimer_ns();
+        for (;;) {
+            uint32_t seen;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.flag_local + 64 + r) : "memory");
+            if (static_cast<int32_t>(seen - epoch) >= 0) break;
             if (globaltimer_ns() - t0 > NVLS_SPIN_TIMEOUT_NS) {
                 *a.error = 1;
                 break;
@@ -322,12 +344,26 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
     }
     rc = load_driver(err, errlen);
     if (rc) return rc;
+    // NVLS needs multicast; the two-shot kernel only needs peer mappings (its barrier then goes through peer stores).
+    bool use_mc = !(getenv("GPUPROBE_NO_MULTICAST") && *getenv("GPUPROBE_NO_MULTICAST") == '1');
     for (auto &d : D) {
         int mc = 0;
-        if (g_drv.DeviceGetAttribute(&mc, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, d.ord) != CUDA_SUCCESS || !mc) {
-            set_err(err, errlen, "device %d does not support NVLink multicast (NVLS)", d.ord);
-            return GPUPROBE_ENOPEER;
-        }
+        if (g_drv.DeviceGetAttribute(&mc, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, d.ord) != CUDA_SUCCESS || !mc) use_mc = false;
+    }
+    if (!use_mc && algo != 1) {
+        set_err(err, errlen, "NVLink multicast (NVLS) is not available on every device; use gpuprobe_allreduce_i32_p2p");
+        return GPUPROBE_ENOPEER;
+    }
+    if (!use_mc) {
+        for (auto &x : D)
+            for (auto &y : D) {
+                int can = 1;
+                if (x.ord != y.ord && (cudaDeviceCanAccessPeer(&can, x.ord, y.ord) != cudaSuccess || !can)) {
+                    (void)cudaGetLastError();
+                    set_err(err, errlen, "device %d cannot access device %d", x.ord, y.ord);
+                    return GPUPROBE_ENOPEER;
+                }
+            }
     }
     std::vector<int> order(nd);
     for (int i = 0; i < nd; ++i) order[i] = i;
@@ -402,7 +438,7 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
     mp.handleTypes = CU_MEM_HANDLE_TYPE_NONE;
     mp.size = payload + NVLS_FLAG_BYTES;
     size_t gran = 0;
-    GP_DRVTRY(g_drv.MulticastGetGranularity(&gran, &mp, CU_MULTICAST_GRANULARITY_MINIMUM));
+    if (use_mc) GP_DRVTRY(g_drv.MulticastGetGranularity(&gran, &mp, CU_MULTICAST_GRANULARITY_MINIMUM));
     for (auto &d : D) {
         CUmemAllocationProp ap;
         std::memset(&ap, 0, sizeof(ap));
@@ -416,9 +452,11 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
     size = ((payload + NVLS_FLAG_BYTES + gran - 1) / gran) * gran;
     mp.size = size;
     const uint64_t flag_off = size - NVLS_FLAG_BYTES;  // last 4 KiB of the allocation, past the payload
-    GP_DRVTRY(g_drv.MulticastCreate(&mc_handle, &mp));
-    mc_created = true;
-    for (auto &d : D) GP_DRVTRY(g_drv.MulticastAddDevice(mc_handle, d.ord));
+    if (use_mc) {
+        GP_DRVTRY(g_drv.MulticastCreate(&mc_handle, &mp));
+        mc_created = true;
+        for (auto &d : D) GP_DRVTRY(g_drv.MulticastAddDevice(mc_handle, d.ord));
+    }
     std::vector<CUmemAccessDesc> access(nd);
     for (int i = 0; i < nd; ++i) {
         access[i].location.type = CU_MEM_LOCATION_TYPE_DEVICE;
@@ -439,8 +477,10 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
         d.uc_mapped = true;
         // every rank may read and write every rank's buffer (the two-shot algorithm; harmless for NVLS)
         GP_DRVTRY(g_drv.MemSetAccess(d.uc, size, access.data(), static_cast<size_t>(nd)));
-        GP_DRVTRY(g_drv.MulticastBindMem(mc_handle, 0, d.mem, 0, size, 0));
-        d.bound = true;
+        if (use_mc) {
+            GP_DRVTRY(g_drv.MulticastBindMem(mc_handle, 0, d.mem, 0, size, 0));
+            d.bound = true;
+        }
         GP_TRY(cudaMalloc(&d.bad, sizeof(unsigned long long)));
         GP_TRY(cudaMalloc(&d.error, sizeof(int)));
         GP_TRY(cudaMemsetAsync(d.bad, 0, sizeof(unsigned long long), d.st->stream));
@@ -452,10 +492,12 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
         GP_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel_fn, NVLS_THREADS, 0));
         d.grid = d.st->sm_count * std::max(1, std::min(per_sm, ctas_per_sm));
     }
-    GP_DRVTRY(g_drv.MemAddressReserve(&mc_va, size, gran, 0, 0));
-    GP_DRVTRY(g_drv.MemMap(mc_va, size, 0, mc_handle, 0));
-    mc_mapped = true;
-    GP_DRVTRY(g_drv.MemSetAccess(mc_va, size, access.data(), static_cast<size_t>(nd)));
+    if (use_mc) {
+        GP_DRVTRY(g_drv.MemAddressReserve(&mc_va, size, gran, 0, 0));
+        GP_DRVTRY(g_drv.MemMap(mc_va, size, 0, mc_handle, 0));
+        mc_mapped = true;
+        GP_DRVTRY(g_drv.MemSetAccess(mc_va, size, access.data(), static_cast<size_t>(nd)));
+    }
     for (auto &d : D) {
         GP_TRY(cudaSetDevice(d.ord));
         GP_TRY(cudaStreamSynchronize(d.st->stream));
@@ -482,6 +524,7 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
             a.nranks = nd;
             a.phases = phases;
             a.algo = algo;
+            a.barrier_peer = use_mc ? 0 : 1;
             a.hybrid_permille = hybrid_permille;
             a.hybrid_nvls_blocks = std::max(1, std::min(d.grid - 1, d.grid * hybrid_block_permille / 1000));
             for (int q = 0; q < NVLS_MAX_PEERS; ++q) a.peer[q] = q < nd ? reinterpret_cast<uint32_t *>(D[q].uc) : nullptr;

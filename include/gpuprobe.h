@@ -267,7 +267,9 @@ GPUPROBE_API int gpuprobe_allreduce_i32_nvls(const gpuprobe_ar_cfg *cfg, gpuprob
 /* (c'') Same launch structure and buffers as the NVLS kernel, but the data moves over plain peer
  * mappings: each rank loads its 1/n slice from every rank (n-1 loads cross NVLink), adds, and
  * stores the sum into every rank's buffer (n-1 stores cross NVLink).  ndev must be 2, 4 or 8.
- * The better choice at 2 ranks, where the switch path moves 1.5x the bytes; no reference counterpart. */
+ * The better choice at 2 ranks, where the switch path moves 1.5x the bytes; no reference counterpart.
+ * Works without NVLS: when a device lacks multicast support (or env GPUPROBE_NO_MULTICAST=1) the
+ * cross-GPU barriers go through per-rank flag slots written with peer stores instead of multimem.red. */
 GPUPROBE_API int gpuprobe_allreduce_i32_p2p(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
 
 /* (c''') Hybrid of the two: the head of each rank's slice goes through the switch (multimem), the

@@ -86,3 +86,15 @@ def test_hybrid_allreduce_kernel_bit_exact(gp, ndev, count):
     for nd in [n for n in (2, 4, 8) if n <= ndev]:
         res = gp.allreduce_i32_hybrid(nd, count, iters=3, warmup=2, seed=8)
         assert res.mismatches == 0 and res.ndev == nd and res.bytes == 4 * count
+
+
+def test_two_shot_allreduce_without_multicast(gp, ndev, monkeypatch):
+    """GPUPROBE_NO_MULTICAST=1: plain peer mappings and a peer-store barrier (boxes without NVLS)."""
+    monkeypatch.setenv("GPUPROBE_NO_MULTICAST", "1")
+    for nd in [n for n in (2, 4, 8) if n <= ndev]:
+        for count in (5, 4096 * 3 + 5, (4 << 20) + 1):
+            res = gp.allreduce_i32_p2p(nd, count, iters=3, warmup=2, seed=9)
+            assert res.mismatches == 0 and res.ndev == nd
+    with pytest.raises(gp.GpuProbeError) as e:
+        gp.allreduce_i32_nvls(2, 1024, iters=1, warmup=1)
+    assert e.value.code == gp.ENOPEER
