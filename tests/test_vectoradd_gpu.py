@@ -273,3 +273,21 @@ def test_full_size_2p32_properties(gp, torch_cuda):
     assert gp.verify_device(dc, n, seed=0, gen_kind=0, stream=s) == 0
     del da, db, dc
     torch.cuda.empty_cache()
+
+
+def test_error_paths_report_codes_not_crashes(gp, torch_cuda):
+    """Out-of-memory, null pointers and a bad device are reported through the status code and message."""
+    with pytest.raises(gp.GpuProbeError) as e:
+        gp.vectoradd(1 << 37, iters=1, warmup=0)  # 3 x 512 GiB
+    assert e.value.code == gp.ENOMEM and "cudaMalloc" in e.value.message
+    with pytest.raises(gp.GpuProbeError) as e:
+        gp.vectoradd_device(0, 0, 0, 16)
+    assert e.value.code == gp.EINVAL
+    with pytest.raises(gp.GpuProbeError) as e:
+        gp.vectoradd(16, dev=63)
+    assert e.value.code == gp.ENODEV
+    with pytest.raises(gp.GpuProbeError) as e:
+        gp.digest_device(0, 16)
+    assert e.value.code == gp.EINVAL
+    # the device is still usable afterwards
+    assert gp.vectoradd(50_000, iters=1, warmup=0).mismatches == 0
