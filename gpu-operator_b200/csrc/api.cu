@@ -88,7 +88,7 @@ extern "C" int gpuprobe_device_info(int dev, gpuprobe_devinfo *out) {
         (void)cudaGetLastError();
         return GPUPROBE_ECUDA;
     }
-    std::snprintf(out->name, sizeof(out->name), "%s", p.name);
+    std::snprintf(out->name, sizeof(out->name), "%.127s", p.name);
     out->cc_major = p.major;
     out->cc_minor = p.minor;
     out->sm_count = p.multiProcessorCount;

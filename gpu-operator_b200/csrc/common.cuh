@@ -93,14 +93,6 @@ __device__ __forceinline__ uint4 ldg128_stream(const void *p) {
                  : "l"(p));
     return r;
 }
-// 128-bit load that is NOT on the .nc path (peer memory written by another GPU just before).
-__device__ __forceinline__ uint4 ldg128_volatile_free(const void *p) {
-    uint4 r;
-    asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-                 : "l"(p));
-    return r;
-}
 __device__ __forceinline__ void stg128_stream(void *p, const uint4 &v) {
     asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
                  "r"(v.w)

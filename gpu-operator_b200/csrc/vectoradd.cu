@@ -13,9 +13,6 @@
 //     mbarrier completion, persistent CTAs (one or two per SM).
 //   * fp32 add is __fadd_rn: IEEE round-to-nearest-even, never fused, denormals kept (no -use_fast_math,
 //     -ftz=false), so results are bit-identical to the host loop c[i] = a[i] + b[i].
-#include <chrono>
-#include <thread>
-
 #include "common.cuh"
 #include "gen.cuh"
 
