@@ -27,11 +27,19 @@ dist.destroy_process_group()
 '''
 
 
+def _free_port():
+    import socket
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
 def _torchrun(args, env_extra=None, timeout=300):
     env = dict(os.environ, BENCH_ROOT=ROOT, OMP_NUM_THREADS="1")
     env.update(env_extra or {})
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
-           "--master-addr", "127.0.0.1", "--master-port", str(29600 + os.getpid() % 300), *args]
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), *args]
     return subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout, cwd=ROOT)
 
 
