@@ -83,6 +83,20 @@ __global__ void __launch_bounds__(T) k_vadd8_pol(const float *__restrict__ a, co
     st8p<SP>(c + base, r);
 }
 
+// vadd with an L2 bulk prefetch of the tile AHEAD tiles further on (one thread per CTA issues it)
+template <int T>
+__global__ void __launch_bounds__(T) k_vadd_pf(const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ c, size_t n_tiles, size_t ahead) {
+    const size_t tile = blockIdx.x;
+    if (threadIdx.x == 0 && tile + ahead < n_tiles) {
+        const float *pa = a + (tile + ahead) * (T * 4), *pb = b + (tile + ahead) * (T * 4);
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(pa), "r"(T * 16) : "memory");
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(pb), "r"(T * 16) : "memory");
+    }
+    const size_t base = tile * (T * 4) + threadIdx.x * 4;
+    float4 x = ld4<L_NC_NA>(a + base), y = ld4<L_NC_NA>(b + base);
+    st4<S_NA>(c + base, add4(x, y));
+}
+
 // read-only (2 streams), write-only, copy
 template <int T, int U>
 __global__ void __launch_bounds__(T) k_read2(const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ c) {
@@ -241,6 +255,11 @@ int main(int argc, char **argv) {
     POL(2, 1, "pol_ld-last_st-first");
     POL(3, 3, "pol_ld-normal_st-normal");
     POL(0, 1, "pol_ld-none_st-first");
+    for (size_t mb : {1, 4, 16, 64, 256}) {
+        const size_t ahead = mb * 1024 * 1024 / 4096;  // tiles of 4 KiB per array
+        E.push_back({"vadd_pfL2_" + std::to_string(mb) + "MB", 12, [ahead](const float *a, const float *b, float *c, size_t n, cudaStream_t s) {
+            k_vadd_pf<256><<<(unsigned)(n / 1024), 256, 0, s>>>(a, b, c, n / 1024, ahead); }});
+    }
     E.push_back({"vadd_bulkstore_t256_u1", 12, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd_bulkstore<256, 1><<<(unsigned)(n / (256 * 1 * 4)), 256, 0, s>>>(a, b, c); }});
     E.push_back({"vadd_bulkstore_t256_u2", 12, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd_bulkstore<256, 2><<<(unsigned)(n / (256 * 2 * 4)), 256, 0, s>>>(a, b, c); }});
     E.push_back({"vadd_bulkstore_t512_u2", 12, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd_bulkstore<512, 2><<<(unsigned)(n / (512 * 2 * 4)), 512, 0, s>>>(a, b, c); }});
