@@ -260,6 +260,14 @@ int main(int argc, char **argv) {
         E.push_back({"vadd_pfL2_" + std::to_string(mb) + "MB", 12, [ahead](const float *a, const float *b, float *c, size_t n, cudaStream_t s) {
             k_vadd_pf<256><<<(unsigned)(n / 1024), 256, 0, s>>>(a, b, c, n / 1024, ahead); }});
     }
+    for (int cl : {2, 4, 8}) {
+        E.push_back({"vadd_cluster" + std::to_string(cl), 12, [cl](const float *a, const float *b, float *c, size_t n, cudaStream_t s) {
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3((unsigned)(n / 1024)); cfg.blockDim = dim3(256); cfg.stream = s;
+            cudaLaunchAttribute at[1]; at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = cl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            cudaLaunchKernelEx(&cfg, k_vadd<256, 1, L_NC_NA, S_NA>, a, b, c); }});
+    }
     E.push_back({"vadd_bulkstore_t256_u1", 12, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd_bulkstore<256, 1><<<(unsigned)(n / (256 * 1 * 4)), 256, 0, s>>>(a, b, c); }});
     E.push_back({"vadd_bulkstore_t256_u2", 12, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd_bulkstore<256, 2><<<(unsigned)(n / (256 * 2 * 4)), 256, 0, s>>>(a, b, c); }});
     E.push_back({"vadd_bulkstore_t512_u2", 12, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd_bulkstore<512, 2><<<(unsigned)(n / (512 * 2 * 4)), 512, 0, s>>>(a, b, c); }});
