@@ -16,9 +16,11 @@
  * (pod phase Succeeded, validator/main.go:1049). This file therefore restates
  * the sample's published algorithm -- C[i] = A[i] + B[i] in IEEE-754 binary32,
  * round-to-nearest-even, followed by a host-side element check -- and is
- * anchored by hand-derived IEEE-754 known answers plus the fixtures in
- * tests/golden/ that tests/golden/make_golden.py generates from an independent
- * numpy restatement (oracle/oracle_np.py).
+ * anchored by hand-derived IEEE-754 known answers, by a binary32 adder written
+ * from the standard in pure integer arithmetic (oracle/ieee754_add.py, checked
+ * against this loop on millions of operand pairs in tests/test_oracle_ieee754.py),
+ * plus the fixtures in tests/golden/ that tests/golden/make_golden.py generates
+ * from an independent numpy restatement (oracle/oracle_np.py).
  *
  * The input generator, the digests and the fabric-probe expected values are
  * NEW (they have no reference counterpart; see DESIGN.md "Generator"): the
