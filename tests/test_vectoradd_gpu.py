@@ -291,3 +291,28 @@ def test_error_paths_report_codes_not_crashes(gp, torch_cuda):
     assert e.value.code == gp.EINVAL
     # the device is still usable afterwards
     assert gp.vectoradd(50_000, iters=1, warmup=0).mismatches == 0
+
+
+def test_concurrent_callers_on_one_device_are_serialised(gp):
+    """The header promises: safe from any OS thread, calls on one device serialised inside the library
+    (a Go validator calls from whichever thread its goroutine happens to run on)."""
+    import threading
+
+    results, errors = {}, []
+
+    def work(i):
+        try:
+            n = (1 << 22) + 1000 * i
+            r = gp.vectoradd(n, iters=3, warmup=1, seed=i, gen_kind=i % 3)
+            results[i] = (n, i, i % 3, r.sum64, r.xor32, r.mismatches)
+        except Exception as e:  # noqa: BLE001
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(6)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    for n, seed, kind, s, x, bad in results.values():
+        assert bad == 0 and (s, x) == oc.vectoradd_digest(n, seed, kind)
