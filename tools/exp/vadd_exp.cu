@@ -212,6 +212,7 @@ int main(int argc, char **argv) {
     int iters = argc > 2 ? atoi(argv[2]) : 20;
     const char *filter = argc > 3 ? argv[3] : "";
     const size_t n = (size_t)1 << lg;
+    if (const char *g = getenv("EXP_L2_FETCH")) { CK(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(g))); size_t v = 0; cudaDeviceGetLimit(&v, cudaLimitMaxL2FetchGranularity); fprintf(stderr, "L2 fetch granularity now %zu\n", v); }
     const size_t PAD = 64u << 20;  // room for offset experiments
     char *pool;
     CK(cudaMalloc(&pool, 3 * (n * 4 + PAD)));
