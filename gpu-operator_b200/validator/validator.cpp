@@ -297,6 +297,8 @@ std::string loadPodSpec(const std::string &path, PodSpec *pod) {
     std::string sub;          // "env" / "limits" / "labels" / "metadata" ...
     std::string pendingEnvName;
     int sectionIndent = -1;
+    std::vector<std::string> *listTarget = nullptr;  // command:/args: given as a block sequence on the next lines
+    int listIndent = 0;
     while (std::getline(in, line)) {
         size_t hash = line.find(" #");
         if (hash != std::string::npos) line = line.substr(0, hash);
@@ -305,6 +307,12 @@ std::string loadPodSpec(const std::string &path, PodSpec *pod) {
         std::string t = trim(line);
         bool dash = t.rfind("- ", 0) == 0;
         if (dash) t = trim(t.substr(2));
+        // block-style sequence under command:/args: ("- sh" / "- -c" / "- vectorAdd")
+        if (listTarget && dash && indent >= listIndent) {
+            listTarget->push_back(unquote(t));
+            continue;
+        }
+        listTarget = nullptr;
         size_t colon = t.find(':');
         if (colon == std::string::npos) continue;
         std::string key = unquote(t.substr(0, colon)), val = trim(t.substr(colon + 1));
@@ -357,8 +365,14 @@ std::string loadPodSpec(const std::string &path, PodSpec *pod) {
             sub.clear();
         } else if (key == "image") pod->image = unquote(val);
         else if (key == "imagePullPolicy") pod->imagePullPolicy = unquote(val);
-        else if (key == "command") pod->initCommand = parseFlowList(val);
-        else if (key == "args") pod->initArgs = parseFlowList(val);
+        else if (key == "command" || key == "args") {
+            std::vector<std::string> &dst = key == "command" ? pod->initCommand : pod->initArgs;
+            dst = parseFlowList(val);
+            if (val.empty()) {  // block sequence follows
+                listTarget = &dst;
+                listIndent = indent;
+            }
+        }
     }
     if (kind != "Pod") return sprintfStr("no kind \"Pod\" is registered in %s (kind: %s)", path.c_str(), kind.c_str());
     if (pod->initArgs.empty()) return sprintfStr("%s: no initContainers[0].args", path.c_str());

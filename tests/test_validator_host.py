@@ -144,6 +144,42 @@ def test_workload_that_never_succeeds_gives_up_like_waitForPod(tmp_path):
     assert r.stderr.count("is curently in Pending phase") == 60  # sic (main.go:1051), podCreationWaitRetries
 
 
+def test_manifest_with_block_style_lists_and_comments(tmp_path):
+    """loadPodSpec (main.go:1061-1081) decodes any YAML; the mirror's reader must at least take both list styles."""
+    d = tmp_path / "manifests"
+    d.mkdir()
+    marker = tmp_path / "ran"
+    (d / "cuda-workload-validation.yaml").write_text(f"""apiVersion: v1
+kind: Pod          # a comment
+metadata:
+    labels:
+        app: nvidia-cuda-validator
+    generateName: "nvidia-cuda-validator-"
+spec:
+    restartPolicy: OnFailure
+    initContainers:
+    - name: cuda-validation
+      image: 'x'
+      command:
+      - sh
+      - "-c"
+      args:
+      - "echo $PROBE_MARK > {marker}"
+      env:
+      - name: PROBE_MARK
+        value: "block-style"
+    containers:
+    - name: nvidia-cuda-validator
+      command: ['sh', '-c']
+      args: ["echo done"]
+""")
+    out = tmp_path / "v"
+    r = run(["-c", "cuda", "-ns", "ns", "-o", str(out)], {"GPUPROBE_MANIFEST_DIR": str(d)})
+    assert r.returncode == 0, r.stderr
+    assert marker.read_text().strip() == "block-style"
+    assert (out / "cuda-ready").exists()
+
+
 def test_missing_manifest_is_an_error(tmp_path):
     r = run(["-c", "cuda", "-ns", "ns", "-o", str(tmp_path / "v")], {"GPUPROBE_MANIFEST_DIR": str(tmp_path / "nowhere")})
     assert r.returncode == 1 and "error validating cuda workload: open " in r.stderr
