@@ -242,6 +242,28 @@ extern "C" int gpuprobe_allreduce_i32(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_re
         GP_TRY(cudaStreamSynchronize(d.st->stream));
         bad_total += h;
     }
+    // The reduced buffers themselves, digested: what a caller compares with a value computed elsewhere (the tests use
+    // the CPU oracle). `mismatches` above is derived from this library's own generator and is a sanity figure only.
+    out->ranks_equal = 1;
+    for (int r = 0; r < nd; ++r) {
+        ArDev &d = D[r];
+        GP_TRY(cudaSetDevice(d.ord));
+        uint64_t s64 = 0;
+        uint32_t x32 = 0;
+        rc = run_digest(*d.st, d.buf, cfg->count, &s64, &x32, d.st->stream, err, errlen);
+        if (rc) {
+            cleanup();
+            return rc;
+        }
+        if (r == 0) {
+            out->sum64 = s64;
+            out->xor32 = x32;
+        } else if (s64 != out->sum64 || x32 != out->xor32) {
+            out->ranks_equal = 0;
+        }
+    }
+    out->rounds = static_cast<uint32_t>(total);
+    out->impl = GPUPROBE_AR_IMPL_NCCL;
     out->mismatches = bad_total;
     out->ms_best = *std::min_element(ms.begin(), ms.end());
     out->ms_median = median_of(ms);
@@ -251,6 +273,10 @@ extern "C" int gpuprobe_allreduce_i32(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_re
     cleanup();
     if (bad_total) {
         set_err(err, errlen, "allreduce: %llu elements differ from the expected sum", (unsigned long long)bad_total);
+        return GPUPROBE_FAIL_VERIFY;
+    }
+    if (!out->ranks_equal) {
+        set_err(err, errlen, "allreduce: the ranks' buffers differ from one another");
         return GPUPROBE_FAIL_VERIFY;
     }
     return GPUPROBE_OK;

@@ -50,10 +50,14 @@ struct NvlsArgs {
     uint32_t barrier_base;  // number of barriers completed before this launch
     int rank, nranks, phases;
     int algo;               // 0: NVLS multimem; 1: two-shot over peer mappings (pull-reduce my slice, push it to everyone);
-                            // 2: hybrid (head of the slice by NVLS, tail by peer mappings, on disjoint CTAs)
+                            // 2: hybrid (head of the slice by NVLS, tail by peer mappings, on disjoint CTAs);
+                            // 3: all-push two-shot (scatter my copy of every slice into its owner's staging area with
+                            //    peer stores, owner adds locally, broadcasts the sum with peer stores: no read crosses a link)
     int hybrid_permille;    // algo 2: share of the slice that goes through the switch, in 1/1000
     int hybrid_nvls_blocks; // algo 2: CTAs [0, this) run the NVLS part, the rest the peer part
     int barrier_peer;       // 1: no multicast on this box -- barrier through per-rank flag slots written with peer stores
+    int st_v4;              // NVLS part: broadcast with 16-byte multimem.st (four sums per store) instead of 4-byte ones
+    uint64_t stage_off;     // algo 3: word offset of the staging area (nranks-1 slices) behind the payload of every rank
     uint32_t *peer[NVLS_MAX_PEERS];  // algo 1: unicast mapping of every rank's buffer (peer[rank] == local)
 };
 
@@ -64,6 +68,13 @@ __device__ __forceinline__ uint32_t mm_ld_reduce_add_u32(const uint32_t *mc) {
 }
 __device__ __forceinline__ void mm_st_u32(uint32_t *mc, uint32_t v) {
     asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(mc), "r"(v) : "memory");
+}
+// Four 32-bit sums in one 16-byte multicast store. The .f32 type only names the container: a store does no
+// arithmetic, the bit patterns travel unchanged (multimem.ld_reduce has no vector form for integer adds).
+__device__ __forceinline__ void mm_st_v4(uint32_t *mc, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(__uint_as_float(x)),
+                 "f"(__uint_as_float(y)), "f"(__uint_as_float(z)), "f"(__uint_as_float(w))
+                 : "memory");
 }
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
     unsigned long long t;
@@ -109,6 +120,69 @@ __device__ __forceinline__ void p2p_reduce_broadcast(const NvlsArgs &a, uint64_t
             asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(w) : "l"(a.peer[r] + i) : "memory");
             acc += w;
         }
+        for (int r = 0; r < NR; ++r) a.peer[r][i] = acc;
+    }
+}
+
+__device__ __forceinline__ uint32_t ld_cg32(const uint32_t *p) {
+    uint32_t w;
+    asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(w) : "l"(p) : "memory");
+    return w;
+}
+
+// All-push two-shot, phase A: for every other rank q, copy MY words of q's slice into the staging slot q keeps for
+// me, with peer stores. Loads are local HBM reads; only posted writes cross NVLink. `per` = slice length (multiple
+// of 32 words); slice q = [q*per, min((q+1)*per, count)); rank r's slot at owner q is slot (r < q ? r : r-1).
+template <int NR>
+__device__ __forceinline__ void push_scatter(const NvlsArgs &a, uint64_t per, uint64_t gtid, uint64_t gstride) {
+    const uint64_t per4 = per / 4, count4 = a.count / 4;
+    for (uint64_t v = gtid; v < per4; v += gstride) {
+        uint4 x[NR];
+#pragma unroll
+        for (int q = 0; q < NR; ++q) {
+            const uint64_t w4 = static_cast<uint64_t>(q) * per4 + v;
+            if (q != a.rank && w4 < count4) x[q] = ld_cg128(a.local + w4 * 4);
+        }
+#pragma unroll
+        for (int q = 0; q < NR; ++q) {
+            const uint64_t w4 = static_cast<uint64_t>(q) * per4 + v;
+            const int slot = a.rank < q ? a.rank : a.rank - 1;
+            if (q != a.rank && w4 < count4) st_128(a.peer[q] + a.stage_off + static_cast<uint64_t>(slot) * per + v * 4, x[q]);
+        }
+    }
+    // the < 4 trailing words of the whole buffer live in one slice
+    for (uint64_t t = count4 * 4 + gtid; t < a.count; t += gstride) {
+        const int q = static_cast<int>(t / per);
+        const int slot = a.rank < q ? a.rank : a.rank - 1;
+        if (q != a.rank) a.peer[q][a.stage_off + static_cast<uint64_t>(slot) * per + (t - static_cast<uint64_t>(q) * per)] = ld_cg32(a.local + t);
+    }
+}
+
+// Phase B: my slice = my own words + the NR-1 staged copies (all local reads), stored into every rank's buffer.
+template <int NR>
+__device__ __forceinline__ void push_add_broadcast(const NvlsArgs &a, uint64_t per, uint64_t lo, uint64_t hi, uint64_t gtid,
+                                                   uint64_t gstride) {
+    const uint64_t lo4 = lo / 4, hi4 = hi / 4;
+    const uint32_t *stage = a.local + a.stage_off;
+    for (uint64_t v = lo4 + gtid; v < hi4; v += gstride) {
+        uint4 x[NR];
+        x[0] = ld_cg128(a.local + v * 4);
+#pragma unroll
+        for (int s = 0; s < NR - 1; ++s) x[s + 1] = ld_cg128(stage + static_cast<uint64_t>(s) * per + (v - lo4) * 4);
+        uint4 acc = x[0];
+#pragma unroll
+        for (int r = 1; r < NR; ++r) {
+            acc.x += x[r].x;
+            acc.y += x[r].y;
+            acc.z += x[r].z;
+            acc.w += x[r].w;
+        }
+#pragma unroll
+        for (int r = 0; r < NR; ++r) st_128(a.peer[r] + v * 4, acc);
+    }
+    for (uint64_t i = max(hi4 * 4, lo) + gtid; i < hi; i += gstride) {
+        uint32_t acc = ld_cg32(a.local + i);
+        for (int s = 0; s < NR - 1; ++s) acc += ld_cg32(stage + static_cast<uint64_t>(s) * per + (i - lo));
         for (int r = 0; r < NR; ++r) a.peer[r][i] = acc;
     }
 }
@@ -176,7 +250,29 @@ __global__ void __launch_bounds__(NVLS_THREADS) nvls_allreduce_kernel(NvlsArgs a
         for (uint64_t j = groups * 4 + gtid; j < a.count; j += gstride) a.local[j] = hash_at(base, j);
     }
 
-    if (a.phases & NVLS_REDUCE) {
+    if ((a.phases & NVLS_REDUCE) && a.algo == 3) {
+        // All-push two-shot. No start barrier across GPUs: phase A only reads this rank's own buffer (complete once
+        // the local grid has finished filling; peers' broadcast stores of the previous round landed before that round's
+        // end barrier) and writes staging slots their owners read only in phase B, after the middle barrier.
+        uint64_t per = (a.count + a.nranks - 1) / a.nranks;
+        per = (per + 31) & ~31ull;
+        const uint64_t lo = min(per * a.rank, a.count), hi = min(lo + per, a.count);
+        grid.sync();
+        switch (a.nranks) {
+        case 2: push_scatter<2>(a, per, gtid, gstride); break;
+        case 4: push_scatter<4>(a, per, gtid, gstride); break;
+        case 8: push_scatter<8>(a, per, gtid, gstride); break;
+        default: break;  // rejected on the host
+        }
+        cross_gpu_barrier(grid, a, bar++);  // every copy of every slice has reached its owner
+        switch (a.nranks) {
+        case 2: push_add_broadcast<2>(a, per, lo, hi, gtid, gstride); break;
+        case 4: push_add_broadcast<4>(a, per, lo, hi, gtid, gstride); break;
+        case 8: push_add_broadcast<8>(a, per, lo, hi, gtid, gstride); break;
+        default: break;
+        }
+        cross_gpu_barrier(grid, a, bar++);  // every slice has been broadcast
+    } else if (a.phases & NVLS_REDUCE) {
         cross_gpu_barrier(grid, a, bar++);  // every rank's inputs are in place (and last round's stores have landed)
         // my slice, rounded so that warps stay on 128-byte lines
         uint64_t per = (a.count + a.nranks - 1) / a.nranks;
@@ -194,6 +290,36 @@ __global__ void __launch_bounds__(NVLS_THREADS) nvls_allreduce_kernel(NvlsArgs a
         auto nvls_part = [&](uint64_t from, uint64_t to, uint64_t bid, uint64_t nb) {
             constexpr uint64_t TILE = static_cast<uint64_t>(NVLS_THREADS) * NVLS_UNROLL;
             const uint64_t n_tiles = (to - from) / TILE;
+            if constexpr (NVLS_UNROLL >= 4) {
+                if (a.st_v4) {
+                    // Same scalar reduce-loads, but each warp owns NVLS_UNROLL*32 consecutive words of the tile, so four
+                    // loads cover 128 consecutive words; a shuffle transpose hands lane l the words 4l..4l+3 of that block
+                    // and the broadcast is one 16-byte multimem.st per lane (a quarter of the store instructions).
+                    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+                    for (uint64_t t = bid; t < n_tiles; t += nb) {
+                        const uint64_t base = from + t * TILE + static_cast<uint64_t>(warp) * (NVLS_UNROLL * 32);
+                        uint32_t v[NVLS_UNROLL];
+#pragma unroll
+                        for (int u = 0; u < NVLS_UNROLL; ++u) v[u] = mm_ld_reduce_add_u32(a.mc + base + u * 32 + lane);
+#pragma unroll
+                        for (int g = 0; g < NVLS_UNROLL / 4; ++g) {
+                            uint32_t o[4];
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const int src = (4 * lane + j) & 31;  // word 4*lane+j of the block sits in lane `src` of load lane>>3
+                                const uint32_t t0 = __shfl_sync(0xffffffffu, v[4 * g + 0], src), t1 = __shfl_sync(0xffffffffu, v[4 * g + 1], src);
+                                const uint32_t t2 = __shfl_sync(0xffffffffu, v[4 * g + 2], src), t3 = __shfl_sync(0xffffffffu, v[4 * g + 3], src);
+                                const int sel = lane >> 3;
+                                o[j] = sel == 0 ? t0 : sel == 1 ? t1 : sel == 2 ? t2 : t3;
+                            }
+                            mm_st_v4(a.mc + base + g * 128 + lane * 4, o[0], o[1], o[2], o[3]);
+                        }
+                    }
+                    for (uint64_t i = from + n_tiles * TILE + bid * NVLS_THREADS + threadIdx.x; i < to; i += nb * NVLS_THREADS)
+                        mm_st_u32(a.mc + i, mm_ld_reduce_add_u32(a.mc + i));
+                    return;
+                }
+            }
             for (uint64_t t = bid; t < n_tiles; t += nb) {
                 const uint64_t base = from + t * TILE + threadIdx.x;
                 uint32_t v[NVLS_UNROLL];
@@ -330,6 +456,7 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
         set_err(err, errlen, "the peer two-shot allreduce is built for 2, 4 or 8 ranks (got %d)", nd);
         return GPUPROBE_EINVAL;
     }
+    const char *algo_name = algo == 0 ? "nvls" : algo == 1 ? "two-shot" : algo == 2 ? "hybrid" : "push two-shot";
     std::vector<NvlsDev> D(nd);
     int rc;
     for (int i = 0; i < nd; ++i) {
@@ -350,7 +477,7 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
         int mc = 0;
         if (g_drv.DeviceGetAttribute(&mc, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, d.ord) != CUDA_SUCCESS || !mc) use_mc = false;
     }
-    if (!use_mc && algo != 1) {
+    if (!use_mc && algo != 1 && algo != 3) {
         set_err(err, errlen, "NVLink multicast (NVLS) is not available on every device; use gpuprobe_allreduce_i32_p2p");
         return GPUPROBE_ENOPEER;
     }
@@ -375,6 +502,8 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
     int unroll = 8, ctas_per_sm = 2;
     if (const char *u = getenv("GPUPROBE_NVLS_UNROLL")) unroll = atoi(u);
     if (const char *c = getenv("GPUPROBE_NVLS_CTAS")) ctas_per_sm = std::max(1, atoi(c));
+    int st_v4 = 0;  // 16-byte multimem.st: measured in profiles/r02_fabric.md
+    if (const char *v = getenv("GPUPROBE_NVLS_ST_V4")) st_v4 = atoi(v) ? 1 : 0;
     int hybrid_permille = 950, hybrid_block_permille = 350;  // centre of the measured plateau at 8 ranks (profiles/r01_fabric.md)
     if (const char *h = getenv("GPUPROBE_HYBRID_PERMILLE")) hybrid_permille = std::max(0, std::min(1000, atoi(h)));
     if (const char *h = getenv("GPUPROBE_HYBRID_BLOCK_PERMILLE")) hybrid_block_permille = std::max(1, std::min(999, atoi(h)));
@@ -384,6 +513,11 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
                                           : reinterpret_cast<const void *>(nvls_allreduce_kernel<2>);
 
     const uint64_t payload = cfg->count * sizeof(uint32_t);
+    // all-push two-shot: behind the payload every rank keeps nd-1 staging slices for its peers' copies of its slice
+    uint64_t per_words = (cfg->count + nd - 1) / nd;
+    per_words = (per_words + 31) & ~31ull;  // as in the kernel
+    const uint64_t stage_off_words = (cfg->count + 31) & ~31ull;
+    const uint64_t data_bytes = algo == 3 ? (stage_off_words + static_cast<uint64_t>(nd - 1) * per_words) * sizeof(uint32_t) : payload;
     CUmemGenericAllocationHandle mc_handle = 0;
     CUdeviceptr mc_va = 0;
     bool mc_created = false, mc_mapped = false;
@@ -436,7 +570,7 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
     std::memset(&mp, 0, sizeof(mp));
     mp.numDevices = static_cast<unsigned>(nd);
     mp.handleTypes = CU_MEM_HANDLE_TYPE_NONE;
-    mp.size = payload + NVLS_FLAG_BYTES;
+    mp.size = data_bytes + NVLS_FLAG_BYTES;
     size_t gran = 0;
     if (use_mc) GP_DRVTRY(g_drv.MulticastGetGranularity(&gran, &mp, CU_MULTICAST_GRANULARITY_MINIMUM));
     for (auto &d : D) {
@@ -449,7 +583,7 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
         GP_DRVTRY(g_drv.MemGetAllocationGranularity(&g2, &ap, CU_MEM_ALLOC_GRANULARITY_MINIMUM));
         gran = std::max(gran, g2);
     }
-    size = ((payload + NVLS_FLAG_BYTES + gran - 1) / gran) * gran;
+    size = ((data_bytes + NVLS_FLAG_BYTES + gran - 1) / gran) * gran;
     mp.size = size;
     const uint64_t flag_off = size - NVLS_FLAG_BYTES;  // last 4 KiB of the allocation, past the payload
     if (use_mc) {
@@ -525,6 +659,8 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
             a.phases = phases;
             a.algo = algo;
             a.barrier_peer = use_mc ? 0 : 1;
+            a.st_v4 = st_v4;
+            a.stage_off = stage_off_words;
             a.hybrid_permille = hybrid_permille;
             a.hybrid_nvls_blocks = std::max(1, std::min(d.grid - 1, d.grid * hybrid_block_permille / 1000));
             for (int q = 0; q < NVLS_MAX_PEERS; ++q) a.peer[q] = q < nd ? reinterpret_cast<uint32_t *>(D[q].uc) : nullptr;
@@ -583,6 +719,28 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
         bad_total += h;
         timed_out |= e;
     }
+    // What the ranks hold now, digested by the same kernel that digests vectorAdd's C: the caller compares it with a
+    // value computed elsewhere (tests: the CPU oracle) -- `mismatches` above comes from this library's own generator.
+    out->ranks_equal = 1;
+    for (int r = 0; r < nd; ++r) {
+        NvlsDev &d = D[r];
+        GP_TRY(cudaSetDevice(d.ord));
+        uint64_t s64 = 0;
+        uint32_t x32 = 0;
+        rc = run_digest(*d.st, reinterpret_cast<const void *>(d.uc), cfg->count, &s64, &x32, d.st->stream, err, errlen);
+        if (rc) {
+            cleanup();
+            return rc;
+        }
+        if (r == 0) {
+            out->sum64 = s64;
+            out->xor32 = x32;
+        } else if (s64 != out->sum64 || x32 != out->xor32) {
+            out->ranks_equal = 0;
+        }
+    }
+    out->rounds = static_cast<uint32_t>(rounds);
+    out->impl = algo == 0 ? GPUPROBE_AR_IMPL_NVLS : algo == 1 ? GPUPROBE_AR_IMPL_P2P : algo == 2 ? GPUPROBE_AR_IMPL_HYBRID : GPUPROBE_AR_IMPL_PUSH;
     out->ndev = nd;
     out->nccl_version = 0;  // not NCCL
     out->bytes = payload;
@@ -594,12 +752,16 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
     out->frac_of_peak = out->busbw_gbps / (cfg->peak_gbps > 0 ? cfg->peak_gbps : 900.0);
     cleanup();
     if (timed_out) {
-        set_err(err, errlen, "allreduce kernel (%s): a cross-GPU barrier timed out", algo == 0 ? "nvls" : algo == 1 ? "two-shot" : "hybrid");
+        set_err(err, errlen, "allreduce kernel (%s): a cross-GPU barrier timed out", algo_name);
         return GPUPROBE_ECUDA;
     }
     if (bad_total) {
-        set_err(err, errlen, "allreduce kernel (%s): %llu elements differ from the expected sum",
-                algo == 0 ? "nvls" : algo == 1 ? "two-shot" : "hybrid", (unsigned long long)bad_total);
+        set_err(err, errlen, "allreduce kernel (%s): %llu elements differ from the expected sum", algo_name,
+                (unsigned long long)bad_total);
+        return GPUPROBE_FAIL_VERIFY;
+    }
+    if (!out->ranks_equal) {
+        set_err(err, errlen, "allreduce kernel (%s): the ranks' buffers differ from one another", algo_name);
         return GPUPROBE_FAIL_VERIFY;
     }
     return GPUPROBE_OK;
@@ -617,4 +779,24 @@ extern "C" int gpuprobe_allreduce_i32_hybrid(const gpuprobe_ar_cfg *cfg, gpuprob
 
 extern "C" int gpuprobe_allreduce_i32_p2p(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen) {
     return allreduce_symmetric(cfg, out, 1, err, errlen);
+}
+
+extern "C" int gpuprobe_allreduce_i32_push(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen) {
+    return allreduce_symmetric(cfg, out, 3, err, errlen);
+}
+
+// The kernel the validator runs when it is not told which: the measured best per rank count
+// (profiles/r02_fabric.md). Falls back to the peer-mapping kernels where NVLS is unavailable.
+extern "C" int gpuprobe_allreduce_i32_auto(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen) {
+    if (!cfg || !out) {
+        set_err(err, errlen, "null cfg/out");
+        return GPUPROBE_EINVAL;
+    }
+    const int nd = cfg->ndev;
+    if (nd != 2 && nd != 4 && nd != 8) return allreduce_symmetric(cfg, out, 0, err, errlen);  // any rank count: NVLS only
+    int algo = nd == 2 ? 1 : 2;
+    if (const char *e = getenv("GPUPROBE_AR_AUTO_ALGO")) algo = std::max(0, std::min(3, atoi(e)));
+    int rc = allreduce_symmetric(cfg, out, algo, err, errlen);
+    if (rc == GPUPROBE_ENOPEER && algo != 1) rc = allreduce_symmetric(cfg, out, 1, err, errlen);  // no multicast on this box
+    return rc;
 }

@@ -16,7 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "lib", "libgpuprobe.so")
 HEADER_PATH = os.path.join(os.path.dirname(HERE), "include", "gpuprobe.h")
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 OK = 0
 FAIL_VERIFY = 1
@@ -83,7 +83,13 @@ class ArCfg(C.Structure):
 class ArResult(C.Structure):
     _fields_ = [("ndev", C.c_int), ("nccl_version", C.c_int), ("bytes", C.c_uint64), ("mismatches", C.c_uint64),
                 ("ms_best", C.c_double), ("ms_median", C.c_double), ("algbw_gbps", C.c_double),
-                ("busbw_gbps", C.c_double), ("frac_of_peak", C.c_double)]
+                ("busbw_gbps", C.c_double), ("frac_of_peak", C.c_double),
+                ("sum64", C.c_uint64), ("xor32", C.c_uint32), ("rounds", C.c_uint32), ("ranks_equal", C.c_int),
+                ("impl", C.c_int)]
+
+
+AR_IMPL_NCCL, AR_IMPL_NVLS, AR_IMPL_P2P, AR_IMPL_HYBRID, AR_IMPL_PUSH = 0, 1, 2, 3, 4
+AR_IMPL_NAMES = {0: "nccl", 1: "nvls", 2: "two_shot", 3: "hybrid", 4: "push"}
 
 
 class GpuProbeError(RuntimeError):
@@ -122,6 +128,8 @@ SIGNATURES = {
     "gpuprobe_allreduce_i32_nvls": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
     "gpuprobe_allreduce_i32_p2p": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
     "gpuprobe_allreduce_i32_hybrid": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
+    "gpuprobe_allreduce_i32_push": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
+    "gpuprobe_allreduce_i32_auto": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
     "gpuprobe_shutdown": (None, []),
 }
 
@@ -293,43 +301,52 @@ def p2p_matrix(ndev: int, bytes_per_pair: int, iters: int = 10, warmup: int = 3,
     return rc, [[cells[s * ndev + t] for t in range(ndev)] for s in range(ndev)]
 
 
-def allreduce_i32(ndev: int, count: int, iters: int = 20, warmup: int = 5, seed: int = 0, devs=None,
-                  peak_gbps: float = 0.0) -> ArResult:
+def _allreduce(symbol: str, ndev: int, count: int, iters: int, warmup: int, seed: int, devs, peak_gbps: float) -> ArResult:
     arr = (C.c_int * ndev)(*devs) if devs is not None else None
     cfg = ArCfg(ndev, arr, count, iters, warmup, seed, peak_gbps)
     out, eb = ArResult(), _errbuf()
-    _check(lib.gpuprobe_allreduce_i32(C.byref(cfg), C.byref(out), eb, len(eb)), "gpuprobe_allreduce_i32", eb)
+    _check(getattr(lib, symbol)(C.byref(cfg), C.byref(out), eb, len(eb)), symbol, eb)
     return out
+
+
+def allreduce_i32(ndev: int, count: int, iters: int = 20, warmup: int = 5, seed: int = 0, devs=None,
+                  peak_gbps: float = 0.0) -> ArResult:
+    """gpuprobe_allreduce_i32: ncclAllReduce(int32, sum) bracketed by the library's fill / verify / digest kernels."""
+    return _allreduce("gpuprobe_allreduce_i32", ndev, count, iters, warmup, seed, devs, peak_gbps)
 
 
 def allreduce_i32_nvls(ndev: int, count: int, iters: int = 20, warmup: int = 5, seed: int = 0, devs=None,
                        peak_gbps: float = 0.0) -> ArResult:
     """gpuprobe_allreduce_i32_nvls: the hand-written multimem (NVLS) allreduce kernel."""
-    arr = (C.c_int * ndev)(*devs) if devs is not None else None
-    cfg = ArCfg(ndev, arr, count, iters, warmup, seed, peak_gbps)
-    out, eb = ArResult(), _errbuf()
-    _check(lib.gpuprobe_allreduce_i32_nvls(C.byref(cfg), C.byref(out), eb, len(eb)), "gpuprobe_allreduce_i32_nvls", eb)
-    return out
+    return _allreduce("gpuprobe_allreduce_i32_nvls", ndev, count, iters, warmup, seed, devs, peak_gbps)
 
 
 def allreduce_i32_p2p(ndev: int, count: int, iters: int = 20, warmup: int = 5, seed: int = 0, devs=None,
                       peak_gbps: float = 0.0) -> ArResult:
     """gpuprobe_allreduce_i32_p2p: two-shot allreduce over peer mappings (2, 4 or 8 ranks)."""
-    arr = (C.c_int * ndev)(*devs) if devs is not None else None
-    cfg = ArCfg(ndev, arr, count, iters, warmup, seed, peak_gbps)
-    out, eb = ArResult(), _errbuf()
-    _check(lib.gpuprobe_allreduce_i32_p2p(C.byref(cfg), C.byref(out), eb, len(eb)), "gpuprobe_allreduce_i32_p2p", eb)
-    return out
+    return _allreduce("gpuprobe_allreduce_i32_p2p", ndev, count, iters, warmup, seed, devs, peak_gbps)
 
 
 def allreduce_i32_hybrid(ndev: int, count: int, iters: int = 20, warmup: int = 5, seed: int = 0, devs=None,
                          peak_gbps: float = 0.0) -> ArResult:
     """gpuprobe_allreduce_i32_hybrid: NVLS for the head of each slice, peer mappings for the tail."""
-    arr = (C.c_int * ndev)(*devs) if devs is not None else None
-    cfg = ArCfg(ndev, arr, count, iters, warmup, seed, peak_gbps)
-    out, eb = ArResult(), _errbuf()
-    _check(lib.gpuprobe_allreduce_i32_hybrid(C.byref(cfg), C.byref(out), eb, len(eb)), "gpuprobe_allreduce_i32_hybrid", eb)
-    return out
+    return _allreduce("gpuprobe_allreduce_i32_hybrid", ndev, count, iters, warmup, seed, devs, peak_gbps)
+
+
+def allreduce_i32_push(ndev: int, count: int, iters: int = 20, warmup: int = 5, seed: int = 0, devs=None,
+                       peak_gbps: float = 0.0) -> ArResult:
+    """gpuprobe_allreduce_i32_push: two-shot with posted writes only (scatter to the owner, add, broadcast)."""
+    return _allreduce("gpuprobe_allreduce_i32_push", ndev, count, iters, warmup, seed, devs, peak_gbps)
+
+
+def allreduce_i32_auto(ndev: int, count: int, iters: int = 20, warmup: int = 5, seed: int = 0, devs=None,
+                       peak_gbps: float = 0.0) -> ArResult:
+    """gpuprobe_allreduce_i32_auto: the library's own choice of hand-written kernel for this rank count."""
+    return _allreduce("gpuprobe_allreduce_i32_auto", ndev, count, iters, warmup, seed, devs, peak_gbps)
+
+
+ALLREDUCE_IMPLS = {"nccl": allreduce_i32, "nvls": allreduce_i32_nvls, "two_shot": allreduce_i32_p2p,
+                   "hybrid": allreduce_i32_hybrid, "push": allreduce_i32_push, "auto": allreduce_i32_auto}
 
 
 def shutdown() -> None:

@@ -10,12 +10,17 @@
 //   on request (env, all default off -- INTEGRATION.md section 4)
 //            GPUPROBE_VADD_ELEMS   HBM bandwidth run on every visible GPU
 //            GPUPROBE_P2P_BYTES    all-pairs NVLink copy+checksum (>= 2 GPUs)
-//            GPUPROBE_AR_COUNT     NCCL int32 allreduce over all visible GPUs
+//            GPUPROBE_AR_COUNT     int32 allreduce over all visible GPUs; GPUPROBE_AR_IMPL = nccl (default) | auto |
+//                                  nvls | p2p | hybrid | push | both.  If NCCL cannot be loaded (the validator image
+//                                  strips the CUDA user libraries) the library's own kernel runs instead and the
+//                                  result says so, unless GPUPROBE_AR_REQUIRE_NCCL=1 makes that a failure.
+//            GPUPROBE_P2P_MODE     serial (default) | serial_push | rounds | rounds_push
 //            GPUPROBE_MIN_HBM_FRAC / GPUPROBE_MIN_LINK_FRAC  fail below this fraction of 8000 / 900 GB/s
 //   Results go to $OUTPUT_DIR/gpuprobe-results.json and .prom when that directory exists.
 #include <sys/stat.h>
 
 #include <algorithm>
+#include <cerrno>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -31,6 +36,23 @@ static unsigned long long envU64(const char *name) {
     const char *v = getenv(name);
     return v && *v ? strtoull(v, nullptr, 0) : 0ull;
 }
+// JSON string body: NODE_NAME comes from the pod spec and is not ours to trust.
+static std::string jsonEscape(const char *s) {
+    std::string out;
+    for (const unsigned char *p = reinterpret_cast<const unsigned char *>(s); *p; ++p) {
+        char buf[8];
+        if (*p == '"' || *p == '\\') {
+            out += '\\';
+            out += static_cast<char>(*p);
+        } else if (*p < 0x20) {
+            snprintf(buf, sizeof(buf), "\\u%04x", *p);
+            out += buf;
+        } else {
+            out += static_cast<char>(*p);
+        }
+    }
+    return out;
+}
 static double envF(const char *name) {
     const char *v = getenv(name);
     return v && *v ? atof(v) : 0.0;
@@ -41,7 +63,11 @@ int main(void) {
     int failed = 0;
     std::ostringstream json, prom;
     const char *node = getenv("NODE_NAME") ? getenv("NODE_NAME") : "";
-    json << "{\"version\":1,\"node\":\"" << node << "\",\"timestamp\":" << static_cast<long long>(time(nullptr));
+    json << "{\"version\":2,\"node\":\"" << jsonEscape(node) << "\",\"timestamp\":" << static_cast<long long>(time(nullptr));
+    if (gpuprobe_abi_version() != GPUPROBE_ABI_VERSION) {
+        fprintf(stderr, "libgpuprobe ABI %d, this binary was built against %d\n", gpuprobe_abi_version(), GPUPROBE_ABI_VERSION);
+        return EXIT_FAILURE;
+    }
 
     // ---- the sample's check ----------------------------------------------------------------
     const int numElements = 50000;
@@ -135,6 +161,11 @@ int main(void) {
         cfg.iters = 10;
         cfg.warmup = 3;
         cfg.mode = GPUPROBE_P2P_SERIAL;
+        if (const char *m = getenv("GPUPROBE_P2P_MODE")) {
+            if (!strcmp(m, "serial_push")) cfg.mode = GPUPROBE_P2P_SERIAL_PUSH;
+            else if (!strcmp(m, "rounds")) cfg.mode = GPUPROBE_P2P_ROUNDS;
+            else if (!strcmp(m, "rounds_push")) cfg.mode = GPUPROBE_P2P_ROUNDS_PUSH;
+        }
         std::vector<gpuprobe_p2p_cell> cells(static_cast<size_t>(ndev) * ndev);
         rc = gpuprobe_p2p_matrix(&cfg, cells.data(), err, sizeof(err));
         std::vector<double> g;
@@ -167,29 +198,42 @@ int main(void) {
         cfg.iters = 20;
         cfg.warmup = 5;
         gpuprobe_ar_result r{};
-        // GPUPROBE_AR_IMPL: "nccl" (default; validates the library path), "nvls" (the hand-written multimem kernel:
-        // no communicator set-up, higher bus bandwidth), "p2p" (two-shot kernel over peer mappings, 2/4/8 GPUs),
-        // "both" (NCCL result reported, NCCL and NVLS must both verify)
+        // GPUPROBE_AR_IMPL: "nccl" (default; validates the library path), "auto" (the library's choice of hand-written
+        // kernel for this rank count; "kernel" is the round-1 spelling), "nvls" / "p2p" / "hybrid" / "push" (one kernel),
+        // "both" (NCCL result reported, NCCL and the auto kernel must both verify)
         const char *impl = getenv("GPUPROBE_AR_IMPL") ? getenv("GPUPROBE_AR_IMPL") : "nccl";
+        const char *implRan = impl;
         if (!strcmp(impl, "nvls")) {
             rc = gpuprobe_allreduce_i32_nvls(&cfg, &r, err, sizeof(err));
         } else if (!strcmp(impl, "p2p")) {
             rc = gpuprobe_allreduce_i32_p2p(&cfg, &r, err, sizeof(err));
         } else if (!strcmp(impl, "hybrid")) {
             rc = gpuprobe_allreduce_i32_hybrid(&cfg, &r, err, sizeof(err));
-        } else if (!strcmp(impl, "kernel")) {
-            // the fastest hand-written kernel for this rank count (profiles/r01_fabric.md)
-            rc = ndev == 2                          ? gpuprobe_allreduce_i32_p2p(&cfg, &r, err, sizeof(err))
-                 : (ndev == 4 || ndev == 8)         ? gpuprobe_allreduce_i32_hybrid(&cfg, &r, err, sizeof(err))
-                                                    : gpuprobe_allreduce_i32_nvls(&cfg, &r, err, sizeof(err));
+        } else if (!strcmp(impl, "push")) {
+            rc = gpuprobe_allreduce_i32_push(&cfg, &r, err, sizeof(err));
+        } else if (!strcmp(impl, "auto") || !strcmp(impl, "kernel")) {
+            rc = gpuprobe_allreduce_i32_auto(&cfg, &r, err, sizeof(err));
         } else {
             rc = gpuprobe_allreduce_i32(&cfg, &r, err, sizeof(err));
-            if (rc == GPUPROBE_OK && !strcmp(impl, "both")) {
+            if (rc == GPUPROBE_ENCCL && envU64("GPUPROBE_AR_REQUIRE_NCCL") == 0) {
+                // No NCCL in this image: the fabric still gets its check, by the library's own kernel.
+                fprintf(stderr, "NCCL unavailable (%s); running the library's allreduce kernel instead\n", err);
+                json << ",\"allreduce_nccl\":\"unavailable\"";
+                implRan = "auto (NCCL unavailable)";
+                rc = gpuprobe_allreduce_i32_auto(&cfg, &r, err, sizeof(err));
+            } else if (rc == GPUPROBE_OK && !strcmp(impl, "both")) {
                 gpuprobe_ar_result r2{};
-                rc = gpuprobe_allreduce_i32_nvls(&cfg, &r2, err, sizeof(err));
-                printf("allreduce int32 x%d (NVLS kernel): busbw %.1f GB/s, %llu mismatches\n", r2.ndev, r2.busbw_gbps,
+                rc = gpuprobe_allreduce_i32_auto(&cfg, &r2, err, sizeof(err));
+                printf("allreduce int32 x%d (library kernel %d): busbw %.1f GB/s, %llu mismatches\n", r2.ndev, r2.impl, r2.busbw_gbps,
                        (unsigned long long)r2.mismatches);
-                json << ",\"allreduce_nvls\":{\"rc\":" << rc << ",\"busbw_gbps\":" << r2.busbw_gbps << ",\"mismatches\":" << r2.mismatches << "}";
+                json << ",\"allreduce_kernel\":{\"rc\":" << rc << ",\"impl\":" << r2.impl << ",\"busbw_gbps\":" << r2.busbw_gbps
+                     << ",\"mismatches\":" << r2.mismatches << ",\"sum64\":" << r2.sum64 << "}";
+                // both paths reduced the same inputs for the same number of rounds: their outputs must be the same bits
+                if (rc == GPUPROBE_OK && r2.rounds == r.rounds && (r2.sum64 != r.sum64 || r2.xor32 != r.xor32)) {
+                    snprintf(err, sizeof(err), "NCCL and the library kernel disagree: %016llx vs %016llx",
+                             (unsigned long long)r.sum64, (unsigned long long)r2.sum64);
+                    rc = GPUPROBE_FAIL_VERIFY;
+                }
             }
         }
         const bool slow = rc == GPUPROBE_OK && minLink > 0 && r.frac_of_peak < minLink;
@@ -197,10 +241,11 @@ int main(void) {
             ++failed;
             fprintf(stderr, "allreduce probe failed: %s %s\n", slow ? gpuprobe_strerror(GPUPROBE_FAIL_BANDWIDTH) : gpuprobe_strerror(rc), err);
         }
-        printf("allreduce int32 x%d: busbw %.1f GB/s, %llu mismatches\n", r.ndev, r.busbw_gbps, (unsigned long long)r.mismatches);
-        json << ",\"allreduce\":{\"rc\":" << rc << ",\"ndev\":" << r.ndev << ",\"bytes\":" << r.bytes << ",\"busbw_gbps\":" << r.busbw_gbps
-             << ",\"mismatches\":" << r.mismatches << "}";
-        promBody << "# HELP gpu_operator_node_cuda_allreduce_busbw_gbps NCCL int32 allreduce bus bandwidth over all GPUs of the node, GB/s\n"
+        printf("allreduce int32 x%d (%s): busbw %.1f GB/s, %llu mismatches\n", r.ndev, implRan, r.busbw_gbps, (unsigned long long)r.mismatches);
+        json << ",\"allreduce\":{\"rc\":" << rc << ",\"impl\":" << r.impl << ",\"ndev\":" << r.ndev << ",\"bytes\":" << r.bytes
+             << ",\"busbw_gbps\":" << r.busbw_gbps << ",\"mismatches\":" << r.mismatches << ",\"rounds\":" << r.rounds
+             << ",\"sum64\":" << r.sum64 << ",\"xor32\":" << r.xor32 << ",\"ranks_equal\":" << r.ranks_equal << "}";
+        promBody << "# HELP gpu_operator_node_cuda_allreduce_busbw_gbps int32 allreduce bus bandwidth over all GPUs of the node, GB/s\n"
                  << "# TYPE gpu_operator_node_cuda_allreduce_busbw_gbps gauge\n"
                  << "gpu_operator_node_cuda_allreduce_busbw_gbps{node=\"@NODE@\"} " << r.busbw_gbps << "\n";
     }
@@ -219,8 +264,14 @@ int main(void) {
                 fwrite(body.data(), 1, body.size(), fp);
                 fclose(fp);
                 rename(tmp.c_str(), path.c_str());
+            } else {
+                fprintf(stderr, "warning: cannot write %s: %s\n", tmp.c_str(), strerror(errno));
             }
         }
+    } else if (vaddElems || p2pBytes || arCount) {
+        // In a cluster this means the workload pod does not mount the validations hostPath (integration/patches/0006):
+        // the probes ran, but the metrics exporter will never see their figures.
+        fprintf(stderr, "warning: %s is not a directory; probe results were not written\n", outDir);
     }
     gpuprobe_shutdown();
     if (failed) return EXIT_FAILURE;

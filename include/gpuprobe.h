@@ -39,7 +39,7 @@ extern "C" {
 #define GPUPROBE_API
 #endif
 
-#define GPUPROBE_ABI_VERSION 1
+#define GPUPROBE_ABI_VERSION 2 /* 2: gpuprobe_ar_result carries the digest of the reduced buffer */
 
 /* ---- status codes ------------------------------------------------------------- */
 #define GPUPROBE_OK 0
@@ -158,7 +158,21 @@ typedef struct gpuprobe_ar_result {
     double algbw_gbps;   /* bytes / ms_median           */
     double busbw_gbps;   /* algbw * 2(n-1)/n            */
     double frac_of_peak;
+    /* ABI 2: what the ranks hold after the last in-place round, so that a caller (the parity tests, the
+     * Go validator) can compare the collective's OUTPUT with a value computed elsewhere instead of
+     * trusting `mismatches`, which the library derives from its own generator. */
+    uint64_t sum64;      /* sum of rank 0's words mod 2^64                                        */
+    uint32_t xor32;      /* xor of the same                                                       */
+    uint32_t rounds;     /* in-place rounds run: every word is ndev^(rounds-1) * sum_r x_r[i]     */
+    int ranks_equal;     /* 1 if every rank's buffer has the digest of rank 0's                   */
+    int impl;            /* GPUPROBE_AR_IMPL_* that produced the result                           */
 } gpuprobe_ar_result;
+
+#define GPUPROBE_AR_IMPL_NCCL 0
+#define GPUPROBE_AR_IMPL_NVLS 1
+#define GPUPROBE_AR_IMPL_P2P 2    /* two-shot: pull-reduce the slice, push the sum            */
+#define GPUPROBE_AR_IMPL_HYBRID 3
+#define GPUPROBE_AR_IMPL_PUSH 4   /* two-shot with posted writes only (scatter, add, broadcast) */
 
 /* ---- library / device queries --------------------------------------------------- */
 
@@ -278,6 +292,18 @@ GPUPROBE_API int gpuprobe_allreduce_i32_p2p(const gpuprobe_ar_cfg *cfg, gpuprobe
  * env GPUPROBE_HYBRID_PERMILLE (share of the data through the switch, default 950) and
  * GPUPROBE_HYBRID_BLOCK_PERMILLE (share of the CTAs on that part, default 350). */
 GPUPROBE_API int gpuprobe_allreduce_i32_hybrid(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
+
+/* (c'''') All-push two-shot: every rank first stores its copy of each slice into a staging area in the slice
+ * owner's memory (peer stores), the owner adds the nd copies out of its own HBM and stores the sum into every
+ * rank's buffer (peer stores again).  No load crosses NVLink, so no read-request packets compete with the data on
+ * the opposite direction of the links; costs (nd-1)/nd of the payload in extra device memory per rank and a
+ * third in-kernel synchronisation.  ndev must be 2, 4 or 8; works with or without multicast.  No reference counterpart. */
+GPUPROBE_API int gpuprobe_allreduce_i32_push(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
+
+/* The hand-written kernel the validator uses when GPUPROBE_AR_IMPL does not name one: the measured best for the
+ * rank count (two-shot over peer mappings at 2 ranks, hybrid at 4 and 8; profiles/r02_fabric.md), falling back to
+ * the two-shot kernel when NVLink multicast is unavailable.  out->impl says which ran.  No reference counterpart. */
+GPUPROBE_API int gpuprobe_allreduce_i32_auto(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
 
 /* Releases cached per-device state (streams, events, scratch).  Optional. */
 GPUPROBE_API void gpuprobe_shutdown(void);

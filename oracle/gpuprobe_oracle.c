@@ -324,6 +324,36 @@ void oracle_allreduce_fill(int32_t *x, uint64_t first, uint64_t n, uint32_t seed
         x[j] = (int32_t)oracle_hash(seed, ORACLE_STREAM_AR(rank), first + j);
 }
 
+/* Digest of what every rank must hold after `rounds` in-place int32 sum-allreduces over `nranks` ranks:
+ * word i = nranks^(rounds-1) * sum_r x_r[i] in wraparound 32-bit arithmetic (each further in-place round adds
+ * nranks equal copies). Threaded because the probe's full size is 2^28 words x 8 ranks of hashing. */
+static void *allreduce_digest_worker(void *p)
+{
+    struct range_job *j = (struct range_job *)p;
+    uint32_t mult = 1;
+    for (int k = 1; k < j->kind; ++k) /* kind carries `rounds` */
+        mult *= (uint32_t)j->src;     /* src carries `nranks` */
+    uint64_t s = 0;
+    uint32_t x = 0;
+    for (uint64_t i = j->first; i < j->first + j->n; ++i) {
+        uint32_t w = 0;
+        for (int r = 0; r < j->src; ++r)
+            w += oracle_hash(j->seed, ORACLE_STREAM_AR(r), i);
+        w *= mult;
+        s += w;
+        x ^= w;
+    }
+    j->sum = s;
+    j->xr = x;
+    return NULL;
+}
+
+void oracle_allreduce_digest(uint64_t first, uint64_t n, uint32_t seed, int nranks, int rounds, int threads,
+                             uint64_t *sum64, uint32_t *xor32)
+{
+    run_range(allreduce_digest_worker, first, n, seed, rounds < 1 ? 1 : rounds, nranks, threads, sum64, xor32);
+}
+
 void oracle_allreduce_expected(int32_t *out, uint64_t first, uint64_t n, uint32_t seed, int nranks)
 {
     for (uint64_t j = 0; j < n; ++j) {

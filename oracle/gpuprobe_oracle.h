@@ -88,6 +88,9 @@ void oracle_p2p_checksum(uint64_t nwords, uint32_t seed, int src, int threads,
 /* allreduce probe: rank r contributes (int32)hash(seed, AR(r), i); expected = wraparound sum */
 void oracle_allreduce_fill(int32_t *x, uint64_t first, uint64_t n, uint32_t seed, int rank);
 void oracle_allreduce_expected(int32_t *out, uint64_t first, uint64_t n, uint32_t seed, int nranks);
+/* sum64 / xor32 of the buffer every rank holds after `rounds` in-place allreduces (threaded) */
+void oracle_allreduce_digest(uint64_t first, uint64_t n, uint32_t seed, int nranks, int rounds, int threads,
+                             uint64_t *sum64, uint32_t *xor32);
 
 /* 1 if the calling thread's FP environment is IEEE (no FTZ/DAZ, round-to-nearest) */
 int oracle_fp_env_ok(void);

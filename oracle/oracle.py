@@ -75,6 +75,8 @@ def lib() -> C.CDLL:
         L.oracle_allreduce_fill.argtypes = [C.POINTER(C.c_int32), u64, u64, u32, i32]
         L.oracle_allreduce_expected.restype = None
         L.oracle_allreduce_expected.argtypes = [C.POINTER(C.c_int32), u64, u64, u32, i32]
+        L.oracle_allreduce_digest.restype = None
+        L.oracle_allreduce_digest.argtypes = [u64, u64, u32, i32, i32, i32, C.POINTER(u64), C.POINTER(u32)]
         L.oracle_fp_env_ok.restype = i32
         L.oracle_fp_env_ok.argtypes = []
         _lib = L
@@ -165,6 +167,13 @@ def allreduce_expected(n: int, seed: int, nranks: int, first: int = 0) -> np.nda
     x = np.empty(n, dtype=np.int32)
     lib().oracle_allreduce_expected(x.ctypes.data_as(C.POINTER(C.c_int32)), first, n, seed, nranks)
     return x
+
+
+def allreduce_digest(n: int, seed: int, nranks: int, rounds: int = 1, first: int = 0, threads: int = 0):
+    """(sum64, xor32) of what every rank holds after `rounds` in-place int32 sum-allreduces."""
+    s, x = C.c_uint64(0), C.c_uint32(0)
+    lib().oracle_allreduce_digest(first, n, seed, nranks, rounds, threads or host_threads(), C.byref(s), C.byref(x))
+    return int(s.value), int(x.value)
 
 
 def fp_env_ok() -> bool:

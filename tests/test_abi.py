@@ -49,7 +49,8 @@ def test_library_holds_sm100a_code_only(gp):
 
 
 def test_abi_version(gp):
-    assert gp.lib.gpuprobe_abi_version() == 1
+    m = re.search(r"#define GPUPROBE_ABI_VERSION\s+(\d+)", open(HEADER).read())
+    assert gp.lib.gpuprobe_abi_version() == int(m.group(1)) == gp.ABI_VERSION == 2
 
 
 def test_struct_layout_matches_c(gp, tmp_path):

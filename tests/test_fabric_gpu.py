@@ -44,21 +44,55 @@ def test_p2p_small_and_explicit_device_list(gp, ndev):
     assert rc == gp.EINVAL
 
 
-@pytest.mark.parametrize("count", [1, 1000, (16 << 20) + 5])
+def assert_reduced_buffer_matches_oracle(res, nd, count, seed, warmup, iters):
+    """The collective's OUTPUT against the CPU oracle: the library returns sum64/xor32 of the buffer rank 0 holds
+    after the last in-place round (and whether every other rank holds the same); the oracle computes the digest of
+    nd^(rounds-1) * sum_r x_r[i] from its own generator.  `mismatches` is the library's self-check and is only
+    looked at second."""
+    assert res.ndev == nd and res.bytes == 4 * count
+    assert res.rounds == max(1, warmup) + iters
+    assert res.ranks_equal == 1
+    assert (res.sum64, res.xor32) == oc.allreduce_digest(count, seed, nd, rounds=res.rounds)
+    if count <= 1 << 16:  # and once more through the array form of the oracle, multiplied out in numpy
+        import numpy as np
+
+        e = oc.allreduce_expected(count, seed, nd).view(np.uint32) * np.uint32(pow(nd, res.rounds - 1, 1 << 32))
+        assert res.sum64 == int(e.sum(dtype=np.uint64)) and res.xor32 == int(np.bitwise_xor.reduce(e))
+    assert res.mismatches == 0
+
+
+AR_COUNTS = [1, 5, 1000, 4096 * 3 + 5, (16 << 20) + 7]
+
+
+@pytest.mark.parametrize("count", AR_COUNTS)
 def test_allreduce_int32_bit_exact(gp, ndev, count):
+    """NCCL int32 sum allreduce (north_star item c): reduced buffers against the oracle, bit for bit."""
     for nd in [n for n in (2, 4, 8) if n <= ndev]:
         res = gp.allreduce_i32(nd, count, iters=3, warmup=2, seed=2)
-        assert res.mismatches == 0 and res.ndev == nd and res.bytes == 4 * count
-        assert res.nccl_version >= 20000
+        assert_reduced_buffer_matches_oracle(res, nd, count, 2, 2, 3)
+        assert res.nccl_version >= 20000 and res.impl == gp.AR_IMPL_NCCL
 
 
-@pytest.mark.parametrize("count", [1, 1000, 4096 * 3 + 5, (16 << 20) + 5])
+@pytest.mark.parametrize("count", AR_COUNTS)
 def test_nvls_allreduce_kernel_bit_exact(gp, ndev, count):
-    """The hand-written multimem kernel (fill -> ld_reduce/st -> verify) against the closed form, and
-    against the oracle on a sample (the verify kernel recomputes the same sum on the device)."""
+    """The hand-written multimem kernel (fill -> ld_reduce/st): reduced buffers against the oracle."""
     for nd in [n for n in (2, 4, 8) if n <= ndev]:
         res = gp.allreduce_i32_nvls(nd, count, iters=3, warmup=2, seed=4)
-        assert res.mismatches == 0 and res.ndev == nd and res.bytes == 4 * count and res.nccl_version == 0
+        assert_reduced_buffer_matches_oracle(res, nd, count, 4, 2, 3)
+        assert res.nccl_version == 0 and res.impl == gp.AR_IMPL_NVLS
+
+
+def test_nvls_allreduce_with_16_byte_multicast_stores(gp, ndev, monkeypatch):
+    """GPUPROBE_NVLS_ST_V4=1: the shuffle-transposed 16-byte multimem.st path, every unroll the library builds."""
+    monkeypatch.setenv("GPUPROBE_NVLS_ST_V4", "1")
+    for unroll in ("4", "8", "16"):
+        monkeypatch.setenv("GPUPROBE_NVLS_UNROLL", unroll)
+        for nd in [n for n in (2, 4, 8) if n <= ndev]:
+            for count in (1000, (4 << 20) + 3):
+                res = gp.allreduce_i32_nvls(nd, count, iters=2, warmup=1, seed=5)
+                assert_reduced_buffer_matches_oracle(res, nd, count, 5, 1, 2)
+                res = gp.allreduce_i32_hybrid(nd, count, iters=2, warmup=1, seed=5)
+                assert_reduced_buffer_matches_oracle(res, nd, count, 5, 1, 2)
 
 
 def test_nvls_and_nccl_agree_on_bandwidth_order_of_magnitude(gp, ndev):
@@ -66,26 +100,46 @@ def test_nvls_and_nccl_agree_on_bandwidth_order_of_magnitude(gp, ndev):
     a = gp.allreduce_i32_nvls(nd, 1 << 26, iters=5, warmup=2)
     b = gp.allreduce_i32(nd, 1 << 26, iters=5, warmup=2)
     assert a.mismatches == 0 and b.mismatches == 0
+    assert (a.sum64, a.xor32) == (b.sum64, b.xor32) == oc.allreduce_digest(1 << 26, 0, nd, rounds=7)
     assert a.busbw_gbps > 0.3 * b.busbw_gbps
 
 
-@pytest.mark.parametrize("count", [1, 5, 1000, 4096 * 3 + 5, (16 << 20) + 7])
+@pytest.mark.parametrize("count", AR_COUNTS)
 def test_p2p_two_shot_allreduce_kernel_bit_exact(gp, ndev, count):
     """Same buffers and barriers as the NVLS kernel, data over plain peer mappings."""
     for nd in [n for n in (2, 4, 8) if n <= ndev]:
         res = gp.allreduce_i32_p2p(nd, count, iters=3, warmup=2, seed=6)
-        assert res.mismatches == 0 and res.ndev == nd and res.bytes == 4 * count
+        assert_reduced_buffer_matches_oracle(res, nd, count, 6, 2, 3)
+        assert res.impl == gp.AR_IMPL_P2P
     with pytest.raises(gp.GpuProbeError) as e:
         gp.allreduce_i32_p2p(3, 1024) if ndev >= 3 else gp.allreduce_i32_p2p(1, 1024)
     assert e.value.code == gp.EINVAL
 
 
-@pytest.mark.parametrize("count", [1, 5, 1000, 4096 * 3 + 5, (16 << 20) + 7])
+@pytest.mark.parametrize("count", AR_COUNTS)
 def test_hybrid_allreduce_kernel_bit_exact(gp, ndev, count):
     """NVLS head + peer-mapping tail on disjoint CTAs of one kernel."""
     for nd in [n for n in (2, 4, 8) if n <= ndev]:
         res = gp.allreduce_i32_hybrid(nd, count, iters=3, warmup=2, seed=8)
-        assert res.mismatches == 0 and res.ndev == nd and res.bytes == 4 * count
+        assert_reduced_buffer_matches_oracle(res, nd, count, 8, 2, 3)
+        assert res.impl == gp.AR_IMPL_HYBRID
+
+
+@pytest.mark.parametrize("count", AR_COUNTS + [31, 32, 33, 64 * 8 + 1])
+def test_push_two_shot_allreduce_kernel_bit_exact(gp, ndev, count):
+    """Posted writes only: scatter into the owner's staging area, local add, broadcast.  Counts around the 32-word
+    slice rounding leave some ranks with an empty slice."""
+    for nd in [n for n in (2, 4, 8) if n <= ndev]:
+        res = gp.allreduce_i32_push(nd, count, iters=3, warmup=2, seed=10)
+        assert_reduced_buffer_matches_oracle(res, nd, count, 10, 2, 3)
+        assert res.impl == gp.AR_IMPL_PUSH
+
+
+def test_auto_allreduce_picks_a_kernel_and_matches_oracle(gp, ndev):
+    for nd in [n for n in (2, 4, 8) if n <= ndev]:
+        res = gp.allreduce_i32_auto(nd, (8 << 20) + 9, iters=2, warmup=1, seed=11)
+        assert_reduced_buffer_matches_oracle(res, nd, (8 << 20) + 9, 11, 1, 2)
+        assert res.impl == (gp.AR_IMPL_P2P if nd == 2 else gp.AR_IMPL_HYBRID)
 
 
 def test_two_shot_allreduce_without_multicast(gp, ndev, monkeypatch):
@@ -94,7 +148,12 @@ def test_two_shot_allreduce_without_multicast(gp, ndev, monkeypatch):
     for nd in [n for n in (2, 4, 8) if n <= ndev]:
         for count in (5, 4096 * 3 + 5, (4 << 20) + 1):
             res = gp.allreduce_i32_p2p(nd, count, iters=3, warmup=2, seed=9)
-            assert res.mismatches == 0 and res.ndev == nd
+            assert_reduced_buffer_matches_oracle(res, nd, count, 9, 2, 3)
+            res = gp.allreduce_i32_push(nd, count, iters=3, warmup=2, seed=9)
+            assert_reduced_buffer_matches_oracle(res, nd, count, 9, 2, 3)
+            res = gp.allreduce_i32_auto(nd, count, iters=2, warmup=1, seed=9)  # falls back to the two-shot kernel
+            assert_reduced_buffer_matches_oracle(res, nd, count, 9, 1, 2)
+            assert res.impl == gp.AR_IMPL_P2P
     with pytest.raises(gp.GpuProbeError) as e:
         gp.allreduce_i32_nvls(2, 1024, iters=1, warmup=1)
     assert e.value.code == gp.ENOPEER

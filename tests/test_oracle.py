@@ -175,3 +175,21 @@ def test_allreduce_golden(golden):
         for r in range(g["nranks"]):
             acc += oc.allreduce_fill(g["n"], g["seed"], r).view(np.uint32)
         assert (acc.view(np.int32) == e).all()
+
+
+def test_allreduce_digest_is_the_digest_of_the_expected_array(golden):
+    """oracle_allreduce_digest (threaded, what the GPU parity tests and bench.py compare with) against the array form
+    multiplied out in numpy, for every golden case, several round counts and a size that splits across threads."""
+    for g in golden["allreduce"]:
+        e = oc.allreduce_expected(g["n"], g["seed"], g["nranks"]).view(np.uint32)
+        assert oc.allreduce_digest(g["n"], g["seed"], g["nranks"], rounds=1)[0] == g["sum64_of_bits"]
+        for rounds in (1, 2, 5, 13):
+            m = e * np.uint32(pow(g["nranks"], rounds - 1, 1 << 32))
+            want = (int(m.sum(dtype=np.uint64)), int(np.bitwise_xor.reduce(m)))
+            assert oc.allreduce_digest(g["n"], g["seed"], g["nranks"], rounds=rounds) == want
+    n = (1 << 18) + 77
+    e = oc.allreduce_expected(n, 7, 8, first=1 << 33).view(np.uint32) * np.uint32(pow(8, 3, 1 << 32))
+    want = (int(e.sum(dtype=np.uint64)), int(np.bitwise_xor.reduce(e)))
+    assert oc.allreduce_digest(n, 7, 8, rounds=4, first=1 << 33, threads=1) == want
+    assert oc.allreduce_digest(n, 7, 8, rounds=4, first=1 << 33, threads=7) == want
+    assert oc.allreduce_digest(0, 7, 8) == (0, 0)

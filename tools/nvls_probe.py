@@ -1,5 +1,7 @@
 #!/usr/bin/env python3
-"""NVLS (multimem) allreduce kernel vs NCCL through the C ABI. Usage: python tools/nvls_probe.py [--counts 20,24,28]"""
+"""Allreduce implementations side by side through the C ABI, one JSON line per (ranks, size).
+Usage: python tools/nvls_probe.py [--counts 10,20,24,28] [--ndevs 2,4,8] [--impls nvls,two_shot,hybrid,push,auto,nccl]
+Every result is compared with the CPU oracle's digest of the reduced buffer (`oracle_ok`)."""
 import argparse
 import json
 import os
@@ -8,11 +10,15 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import __graft_entry__ as ge  # noqa: E402
+from oracle import oracle as oc  # noqa: E402  (a measurement tool, not the product: it may use the checker)
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--counts", default="10,20,24,28")
 ap.add_argument("--ndevs", default="")
-ap.add_argument("--skip-nccl", action="store_true")
+ap.add_argument("--impls", default="nvls,two_shot,hybrid,push,auto,nccl")
+ap.add_argument("--iters", type=int, default=20)
+ap.add_argument("--warmup", type=int, default=5)
+ap.add_argument("--tag", default="")
 args = ap.parse_args()
 gp = ge.load_package().gpuprobe
 n = gp.device_count()
@@ -20,22 +26,17 @@ ndevs = [int(x) for x in args.ndevs.split(",") if x] or [k for k in (2, 4, 8) if
 for nd in ndevs:
     for lg in [int(x) for x in args.counts.split(",")]:
         row = {"ndev": nd, "bytes": 4 << lg}
-        try:
-            a = gp.allreduce_i32_nvls(nd, 1 << lg, iters=20, warmup=5)
-            row["nvls"] = {"us": round(a.ms_median * 1e3, 1), "busbw": round(a.busbw_gbps, 1), "algbw": round(a.algbw_gbps, 1), "mism": a.mismatches}
-        except gp.GpuProbeError as e:
-            row["nvls"] = {"error": str(e)}
-        try:
-            c = gp.allreduce_i32_p2p(nd, 1 << lg, iters=20, warmup=5)
-            row["p2p2shot"] = {"us": round(c.ms_median * 1e3, 1), "busbw": round(c.busbw_gbps, 1), "mism": c.mismatches}
-        except gp.GpuProbeError as e:
-            row["p2p2shot"] = {"error": str(e)}
-        try:
-            h = gp.allreduce_i32_hybrid(nd, 1 << lg, iters=20, warmup=5)
-            row["hybrid"] = {"us": round(h.ms_median * 1e3, 1), "busbw": round(h.busbw_gbps, 1), "mism": h.mismatches}
-        except gp.GpuProbeError as e:
-            row["hybrid"] = {"error": str(e)}
-        if not args.skip_nccl:
-            b = gp.allreduce_i32(nd, 1 << lg, iters=20, warmup=5)
-            row["nccl"] = {"us": round(b.ms_median * 1e3, 1), "busbw": round(b.busbw_gbps, 1), "mism": b.mismatches}
+        if args.tag:
+            row["tag"] = args.tag
+        want = {}
+        for impl in args.impls.split(","):
+            try:
+                r = gp.ALLREDUCE_IMPLS[impl](nd, 1 << lg, iters=args.iters, warmup=args.warmup)
+                if r.rounds not in want:
+                    want[r.rounds] = oc.allreduce_digest(1 << lg, 0, nd, rounds=r.rounds)
+                row[impl] = {"us": round(r.ms_median * 1e3, 1), "busbw": round(r.busbw_gbps, 1), "algbw": round(r.algbw_gbps, 1),
+                             "frac_of_900": round(r.frac_of_peak, 4), "mism": r.mismatches, "impl": gp.AR_IMPL_NAMES[r.impl],
+                             "oracle_ok": (r.sum64, r.xor32) == want[r.rounds] and r.ranks_equal == 1}
+            except gp.GpuProbeError as e:
+                row[impl] = {"error": str(e)}
         print(json.dumps(row), flush=True)
