@@ -12,13 +12,18 @@ static std::mutex g_init_mu;
 
 DeviceState &device_state(int dev) { return g_state[dev]; }
 
+static std::atomic<int> g_device_count{-1};  // cached after the first successful query (devices do not come and go)
+
 int use_device(int dev, DeviceState **out, char *err, size_t errlen) {
-    int count = 0;
-    cudaError_t e = cudaGetDeviceCount(&count);
-    if (e != cudaSuccess || count == 0) {
-        set_err(err, errlen, "no CUDA device available: %s", e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
-        (void)cudaGetLastError();
-        return GPUPROBE_ENODEV;
+    int count = g_device_count.load(std::memory_order_acquire);
+    if (count < 0) {
+        cudaError_t e = cudaGetDeviceCount(&count);
+        if (e != cudaSuccess || count == 0) {
+            set_err(err, errlen, "no CUDA device available: %s", e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+            (void)cudaGetLastError();
+            return GPUPROBE_ENODEV;
+        }
+        g_device_count.store(count, std::memory_order_release);
     }
     if (dev < 0 || dev >= count || dev >= MAX_DEVICES) {
         set_err(err, errlen, "device %d out of range (0..%d)", dev, count - 1);
@@ -26,8 +31,12 @@ int use_device(int dev, DeviceState **out, char *err, size_t errlen) {
     }
     GP_CUDA(cudaSetDevice(dev));
     DeviceState &st = g_state[dev];
+    if (st.inited.load(std::memory_order_acquire)) {  // the launch-bound path: no lock, no driver query
+        *out = &st;
+        return GPUPROBE_OK;
+    }
     std::lock_guard<std::mutex> lock(g_init_mu);
-    if (!st.inited) {
+    if (!st.inited.load(std::memory_order_relaxed)) {
         cudaDeviceProp p{};
         GP_CUDA(cudaGetDeviceProperties(&p, dev));
         if (p.major != 10) {
@@ -42,12 +51,36 @@ int use_device(int dev, DeviceState **out, char *err, size_t errlen) {
         st.cc_minor = p.minor;
         st.l2_bytes = static_cast<size_t>(p.l2CacheSize);
         st.max_smem_optin = static_cast<int>(p.sharedMemPerBlockOptin);
-        GP_CUDA(cudaStreamCreateWithFlags(&st.stream, cudaStreamNonBlocking));
-        for (auto &s : st.copy_streams) GP_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
-        st.inited = true;
+        cudaStream_t made[1 + BUF_MAX_SLOTS] = {};
+        for (int i = 0; i < 1 + BUF_MAX_SLOTS; ++i) {
+            cudaError_t e = cudaStreamCreateWithFlags(&made[i], cudaStreamNonBlocking);
+            if (e != cudaSuccess) {  // leave nothing half-built behind
+                for (int j = 0; j < i; ++j) cudaStreamDestroy(made[j]);
+                set_err(err, errlen, "cudaStreamCreateWithFlags failed: %s", cudaGetErrorString(e));
+                (void)cudaGetLastError();
+                return GPUPROBE_ECUDA;
+            }
+        }
+        st.stream = made[0];
+        for (int i = 0; i < BUF_MAX_SLOTS; ++i) st.copy_streams[i] = made[1 + i];
+        st.inited.store(true, std::memory_order_release);
     }
     *out = &st;
     return GPUPROBE_OK;
+}
+
+void free_buf_slots(DeviceState &st) {
+    for (auto &sl : st.buf_slots) {
+        cudaFree(sl.d_a);
+        cudaFree(sl.d_b);
+        cudaFree(sl.d_c);
+        if (sl.h_a) cudaFreeHost(sl.h_a);
+        if (sl.h_b) cudaFreeHost(sl.h_b);
+        if (sl.h_c) cudaFreeHost(sl.h_c);
+        if (sl.done) cudaEventDestroy(sl.done);
+        sl = BufSlot{};
+    }
+    (void)cudaGetLastError();
 }
 
 static int host_threads(int want) {
@@ -190,16 +223,20 @@ extern "C" void gpuprobe_shutdown(void) {
     std::lock_guard<std::mutex> lock(g_init_mu);
     for (int d = 0; d < MAX_DEVICES; ++d) {
         DeviceState &st = g_state[d];
-        if (!st.inited) continue;
+        if (!st.inited.load(std::memory_order_acquire)) continue;
         std::lock_guard<std::mutex> dl(st.mu);
+        std::lock_guard<std::mutex> sl(st.scratch_mu);
         if (cudaSetDevice(d) == cudaSuccess) {
+            cudaDeviceSynchronize();
+            free_buf_slots(st);
+            cudaFree(st.scratch);
             cudaStreamDestroy(st.stream);
             for (auto &s : st.copy_streams) cudaStreamDestroy(s);
         }
         (void)cudaGetLastError();
+        st.scratch = nullptr;
         st.stream = nullptr;
         for (auto &s : st.copy_streams) s = nullptr;
-        st.inited = false;
-        st.func_attrs_set = false;
+        st.inited.store(false, std::memory_order_release);
     }
 }

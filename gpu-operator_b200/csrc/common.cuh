@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
@@ -37,17 +38,36 @@ inline void set_err(char *err, size_t errlen, const char *fmt, ...) {
         }                                                                                          \
     } while (0)
 
+// One staging slot of the host-buffer path (gpuprobe_vectoradd_buffers): device chunks of A, B, C, pinned bounce
+// buffers for pageable callers, and the event that says the slot's C has landed. Cached per device, grown on demand.
+constexpr int BUF_MAX_SLOTS = 4;  // = number of copy streams per device
+struct BufSlot {
+    float *d_a = nullptr, *d_b = nullptr, *d_c = nullptr;
+    float *h_a = nullptr, *h_b = nullptr, *h_c = nullptr;
+    cudaEvent_t done = nullptr;
+    uint64_t dev_cap = 0, host_cap = 0;       // elements the device / pinned buffers can hold
+    uint64_t pending_off = 0, pending_n = 0;  // chunk whose C still sits in h_c
+};
+
 struct DeviceState {
-    std::mutex mu;  // calls that use the same device are serialised
-    bool inited = false;
+    std::mutex mu;  // the synchronous probes (vectoradd, vectoradd_buffers, p2p, allreduce) on one device are serialised
+    std::atomic<bool> inited{false};
     int dev = -1;
     int sm_count = 0;
     int cc_major = 0, cc_minor = 0;
     size_t l2_bytes = 0;
     int max_smem_optin = 0;
     cudaStream_t stream = nullptr;       // compute / timing stream of the probes
-    cudaStream_t copy_streams[4] = {};   // pipelined H2D / kernel / D2H chunks of the buffers path
-    bool func_attrs_set = false;
+    cudaStream_t copy_streams[BUF_MAX_SLOTS] = {};   // pipelined H2D / kernel / D2H chunks of the buffers path
+    std::once_flag func_attrs_once;
+    cudaError_t func_attrs_err = cudaSuccess;
+    // Cached device scratch of the digest and verify kernels (partials + result + a mismatch counter). Allocated at the
+    // first digest/verify on the device, kept until gpuprobe_shutdown; scratch_mu serialises its users, whichever stream
+    // they run on (each of them synchronises its stream before it releases the lock).
+    std::mutex scratch_mu;
+    void *scratch = nullptr;
+    // Cached staging of the host-buffer path; guarded by `mu`.
+    BufSlot buf_slots[BUF_MAX_SLOTS];
 };
 
 DeviceState &device_state(int dev);
@@ -55,6 +75,9 @@ DeviceState &device_state(int dev);
 // Selects `dev`, checks it is an sm_100 part and lazily creates the cached state.
 // Returns GPUPROBE_OK or an error code with the message in err.
 int use_device(int dev, DeviceState **out, char *err, size_t errlen);
+
+// Frees the cached staging of the host-buffer path (device current, st.mu held). Defined in api.cu.
+void free_buf_slots(DeviceState &st);
 
 // Shared launchers (defined in vectoradd.cu).
 int launch_vadd(DeviceState &st, const float *a, const float *b, float *c, uint64_t n, int variant,

@@ -33,7 +33,10 @@
 //     returns, so calls made through this entry point never overlap each other.  Separate
 //     processes do not interfere: each has its own copy of the array.
 //   * The first call on a device resolves the array's device address (set-up, once per device).
-//     Make that first call outside any stream capture.
+//     Make that first call outside any stream capture -- and early: under CUDA's default lazy
+//     module loading the address look-up can be the moment the library's device image (this
+//     array included) is placed on the GPU, so a caller that waits until memory is exhausted
+//     may see the set-up itself fail.  A call with n = 0 at start-up does the set-up and nothing else.
 #include "common.cuh"
 
 namespace gp {

@@ -1,14 +1,22 @@
 // p2p.cu -- probe (b): all-pairs NVLink copy + checksum.  New capability: the reference never
 // touches a second GPU (its only kernel runs on device 0; SURVEY.md section 2 kernel inventory).
 //
-// For a directed pair src -> dst the kernel runs on dst and LOADS src's buffer through the
-// peer mapping (the loads are the NVLink traffic: requests travel dst -> src, data returns
-// src -> dst through NVSwitch), stores the words into a local buffer and reduces
-// sum(uint32) -> uint64 and xor with warp shuffles.  The copy and the checksum are one pass:
-// 1 x bytes over NVLink, 1 x bytes of local HBM writes, nothing re-read.
+// For a directed pair src -> dst the kernel runs on dst and READS src's buffer through the peer
+// mapping (the reads are the NVLink traffic: requests travel dst -> src, data returns src -> dst
+// through NVSwitch), writes the words into a local buffer and reduces sum(uint32) -> uint64 and
+// xor with warp shuffles.  The copy and the checksum are one pass: 1 x bytes over NVLink, 1 x
+// bytes of local HBM writes, nothing re-read.  PUSH modes run the same kernel on src with the
+// peer pointer on the store side.
 //
-// Remote latency is microseconds, so every thread keeps UNROLL 128-bit loads in flight and
-// the grid is persistent (k CTAs per SM) to put tens of MB in flight chip-wide.
+// Default kernel (round 2): a cp.async.bulk ring.  One thread per CTA asks the SM's copy engine for
+// 32 KiB at a time (global -> shared, mbarrier transaction count), all threads checksum the stage out
+// of shared memory, the same thread sends it on with a bulk store.  Measured against the register
+// path on a loaded fabric (both directions busy, profiles/r02_fabric.md): pull 667 vs 629 GB/s per
+// direction, push 700 vs 695; one pair alone 776 vs 766.  The register-path kernel (every thread
+// keeps 8 x 128-bit loads in flight) stays as env GPUPROBE_P2P_KERNEL=ldst.
+//
+// Remote latency is microseconds, so tens of MB must be in flight chip-wide: 2 CTAs per SM x 3
+// stages x 32 KiB = 28 MB on 148 SMs.
 #include <future>
 
 #include "common.cuh"
@@ -110,6 +118,146 @@ p2p_copy_checksum_kernel(const uint4 *__restrict__ src_peer, uint4 *__restrict__
     }
 }
 
+// ---- the bulk-copy (TMA engine) ring ------------------------------------------------------------------
+constexpr int P2PB_THREADS = 128;
+constexpr int P2PB_CHUNK = 32768;  // bytes per bulk request
+constexpr int P2PB_STAGES = 3;
+constexpr int P2PB_CTAS_PER_SM = 2;
+constexpr size_t P2PB_SMEM = static_cast<size_t>(P2PB_STAGES) * P2PB_CHUNK + P2PB_STAGES * sizeof(uint64_t);
+
+__device__ __forceinline__ uint32_t p2p_smem_u32(const void *p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+// Iteration k of a CTA (stage s = k % STAGES): wait full[s]; every thread adds its share of the stage into its
+// checksum registers (LDS.128); __syncthreads; thread 0 issues the bulk store of stage s and then refills the stage
+// that iteration k-1 stored -- after cp.async.bulk.wait_group.read 1 has shown that store has finished reading it --
+// with chunk k+STAGES-1. So STAGES-1 loads and up to 2 stores are in flight per CTA at any time.
+__global__ void __launch_bounds__(P2PB_THREADS)
+p2p_bulk_copy_checksum_kernel(const unsigned char *__restrict__ src, unsigned char *__restrict__ dst, uint64_t bytes,
+                              P2PScratch *scr) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem + static_cast<size_t>(P2PB_STAGES) * P2PB_CHUNK);
+    const uint64_t n_chunks = bytes / P2PB_CHUNK;
+    const uint64_t first = blockIdx.x, stride = gridDim.x;
+    const uint64_t mine = first < n_chunks ? (n_chunks - first + stride - 1) / stride : 0;
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < P2PB_STAGES; ++s)
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(p2p_smem_u32(&full[s])), "r"(1) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto load = [&](uint64_t k) {  // thread 0 only
+        const int s = static_cast<int>(k % P2PB_STAGES);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(p2p_smem_u32(&full[s])), "r"(P2PB_CHUNK) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         p2p_smem_u32(smem + static_cast<size_t>(s) * P2PB_CHUNK)),
+                     "l"(src + (first + k * stride) * P2PB_CHUNK), "r"(P2PB_CHUNK), "r"(p2p_smem_u32(&full[s]))
+                     : "memory");
+    };
+    if (threadIdx.x == 0)
+        for (uint64_t k = 0; k < static_cast<uint64_t>(P2PB_STAGES - 1) && k < mine; ++k) load(k);
+
+    uint64_t sum = 0;
+    uint32_t x = 0;
+    for (uint64_t k = 0; k < mine; ++k) {
+        const int s = static_cast<int>(k % P2PB_STAGES);
+        const uint32_t parity = static_cast<uint32_t>((k / P2PB_STAGES) & 1u);
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "W_%=:\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+            "@!p bra W_%=;\n"
+            "}\n" ::"r"(p2p_smem_u32(&full[s])),
+            "r"(parity)
+            : "memory");
+        const uint4 *p = reinterpret_cast<const uint4 *>(smem + static_cast<size_t>(s) * P2PB_CHUNK);
+#pragma unroll 4
+        for (int i = threadIdx.x; i < P2PB_CHUNK / 16; i += P2PB_THREADS) {
+            const uint4 v = p[i];
+            sum += static_cast<uint64_t>(v.x) + v.y + static_cast<uint64_t>(v.z) + v.w;
+            x ^= v.x ^ v.y ^ v.z ^ v.w;
+        }
+        __syncthreads();  // everyone has read stage s (and, one iteration ago, the stage about to be refilled)
+        if (threadIdx.x == 0) {
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst + (first + k * stride) * P2PB_CHUNK),
+                         "r"(p2p_smem_u32(smem + static_cast<size_t>(s) * P2PB_CHUNK)), "r"(P2PB_CHUNK)
+                         : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            if (k + P2PB_STAGES - 1 < mine) {
+                asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                load(k + P2PB_STAGES - 1);
+            }
+        }
+    }
+    if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+
+    // ragged remainder (< one chunk), 16 bytes at a time through registers
+    const uint64_t n16 = bytes / 16;
+    const uint4 *src16 = reinterpret_cast<const uint4 *>(src);
+    uint4 *dst16 = reinterpret_cast<uint4 *>(dst);
+    for (uint64_t i = n_chunks * (P2PB_CHUNK / 16) + static_cast<uint64_t>(blockIdx.x) * P2PB_THREADS + threadIdx.x; i < n16;
+         i += static_cast<uint64_t>(gridDim.x) * P2PB_THREADS) {
+        const uint4 v = ldg128_stream(src16 + i);
+        stg128_stream(dst16 + i, v);
+        sum += static_cast<uint64_t>(v.x) + v.y + static_cast<uint64_t>(v.z) + v.w;
+        x ^= v.x ^ v.y ^ v.z ^ v.w;
+    }
+
+    __shared__ uint64_t sh_s[P2PB_THREADS / 32];
+    __shared__ uint32_t sh_x[P2PB_THREADS / 32];
+    __shared__ bool is_last;
+    sum = warp_sum_u64(sum);
+    x = warp_xor_u32(x);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) {
+        sh_s[warp] = sum;
+        sh_x[warp] = x;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint64_t bs = 0;
+        uint32_t bx = 0;
+        for (int i = 0; i < P2PB_THREADS / 32; ++i) {
+            bs += sh_s[i];
+            bx ^= sh_x[i];
+        }
+        scr->partial_sum[blockIdx.x] = bs;
+        scr->partial_xor[blockIdx.x] = bx;
+        __threadfence();
+        is_last = (atomicAdd(&scr->ticket, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (is_last) {  // the last CTA to finish folds the partials
+        __threadfence();
+        uint64_t ts = 0;
+        uint32_t tx = 0;
+        for (unsigned int i = threadIdx.x; i < gridDim.x; i += blockDim.x) {
+            ts += *(volatile uint64_t *)(scr->partial_sum + i);
+            tx ^= *(volatile uint32_t *)(scr->partial_xor + i);
+        }
+        ts = warp_sum_u64(ts);
+        tx = warp_xor_u32(tx);
+        __syncthreads();
+        if (lane == 0) {
+            sh_s[warp] = ts;
+            sh_x[warp] = tx;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint64_t bs = 0;
+            uint32_t bx = 0;
+            for (int i = 0; i < P2PB_THREADS / 32; ++i) {
+                bs += sh_s[i];
+                bx ^= sh_x[i];
+            }
+            scr->out_sum = bs;
+            scr->out_xor = bx;
+            scr->ticket = 0;
+        }
+    }
+}
+
 struct P2PDev {
     int ord = -1;
     DeviceState *st = nullptr;
@@ -120,6 +268,12 @@ struct P2PDev {
     uint64_t exp_sum = 0;
     uint32_t exp_xor = 0;
 };
+
+static int p2p_bulk_grid(const DeviceState &st, uint64_t bytes) {
+    const uint64_t chunks = bytes / P2PB_CHUNK + 1;
+    const uint64_t cap = std::min<uint64_t>(static_cast<uint64_t>(st.sm_count) * P2PB_CTAS_PER_SM, P2P_MAX_BLOCKS);
+    return static_cast<int>(std::max<uint64_t>(1, std::min(chunks, cap)));
+}
 
 static int p2p_grid(const DeviceState &st, uint64_t n16) {
     const uint64_t tiles = n16 / (static_cast<uint64_t>(P2P_THREADS) * P2P_UNROLL) + 1;
@@ -243,6 +397,14 @@ extern "C" int gpuprobe_p2p_matrix(const gpuprobe_p2p_cfg *cfg, gpuprobe_p2p_cel
 
     // PULL (default): the kernel runs on dst and loads src's buffer over NVLink. PUSH: it runs on src, loads its own
     // buffer and stores into dst's landing buffer over NVLink (posted writes need no request packets on the way back).
+    const char *kern_env = getenv("GPUPROBE_P2P_KERNEL");
+    const bool bulk = !(kern_env && !strcmp(kern_env, "ldst"));
+    if (bulk)
+        for (auto &d : D) {
+            GP_TRY(cudaSetDevice(d.ord));
+            GP_TRY(cudaFuncSetAttribute(p2p_bulk_copy_checksum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        static_cast<int>(P2PB_SMEM)));
+        }
     const bool push = cfg->mode == GPUPROBE_P2P_ROUNDS_PUSH || cfg->mode == GPUPROBE_P2P_SERIAL_PUSH;
     const bool serial = cfg->mode == GPUPROBE_P2P_SERIAL || cfg->mode == GPUPROBE_P2P_SERIAL_PUSH;
     auto runner = [&](int s, int t) { return push ? s : t; };
@@ -252,8 +414,12 @@ extern "C" int gpuprobe_p2p_matrix(const gpuprobe_p2p_cfg *cfg, gpuprobe_p2p_cel
         cudaError_t e = cudaSetDevice(dd.ord);
         if (e != cudaSuccess) return e;
         if (timed && (e = cudaEventRecord(dd.ev0, dd.st->stream)) != cudaSuccess) return e;
-        p2p_copy_checksum_kernel<<<p2p_grid(*dd.st, n16), P2P_THREADS, 0, dd.st->stream>>>(
-            reinterpret_cast<const uint4 *>(D[s].src), reinterpret_cast<uint4 *>(D[t].dst), n16, dd.scr);
+        if (bulk)
+            p2p_bulk_copy_checksum_kernel<<<p2p_bulk_grid(*dd.st, bytes), P2PB_THREADS, P2PB_SMEM, dd.st->stream>>>(
+                reinterpret_cast<const unsigned char *>(D[s].src), reinterpret_cast<unsigned char *>(D[t].dst), bytes, dd.scr);
+        else
+            p2p_copy_checksum_kernel<<<p2p_grid(*dd.st, n16), P2P_THREADS, 0, dd.st->stream>>>(
+                reinterpret_cast<const uint4 *>(D[s].src), reinterpret_cast<uint4 *>(D[t].dst), n16, dd.scr);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if (timed) e = cudaEventRecord(dd.ev1, dd.st->stream);
         return e;

@@ -425,13 +425,21 @@ constexpr int TMA16_STAGES = 4, TMA16_TILE = 4096;
 constexpr int TMA8_STAGES = 4, TMA8_TILE = 2048;
 constexpr size_t tma_smem_bytes(int tile_f, int stages) { return 3u * stages * tile_f * 4u + stages * 8u; }
 
+// Opt-in shared memory of the TMA variants: once per device, whichever thread gets there first (the device is current).
 static int set_func_attrs(DeviceState &st, char *err, size_t errlen) {
-    if (st.func_attrs_set) return GPUPROBE_OK;
-    GP_CUDA(cudaFuncSetAttribute(vadd_tma_kernel<TMA16_TILE, TMA16_STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 static_cast<int>(tma_smem_bytes(TMA16_TILE, TMA16_STAGES))));
-    GP_CUDA(cudaFuncSetAttribute(vadd_tma_kernel<TMA8_TILE, TMA8_STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 static_cast<int>(tma_smem_bytes(TMA8_TILE, TMA8_STAGES))));
-    st.func_attrs_set = true;
+    std::call_once(st.func_attrs_once, [&st]() {
+        cudaError_t e = cudaFuncSetAttribute(vadd_tma_kernel<TMA16_TILE, TMA16_STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             static_cast<int>(tma_smem_bytes(TMA16_TILE, TMA16_STAGES)));
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(vadd_tma_kernel<TMA8_TILE, TMA8_STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     static_cast<int>(tma_smem_bytes(TMA8_TILE, TMA8_STAGES)));
+        st.func_attrs_err = e;
+    });
+    if (st.func_attrs_err != cudaSuccess) {
+        set_err(err, errlen, "cudaFuncSetAttribute failed: %s", cudaGetErrorString(st.func_attrs_err));
+        (void)cudaGetLastError();
+        return GPUPROBE_ECUDA;
+    }
     return GPUPROBE_OK;
 }
 
@@ -554,7 +562,19 @@ static int digest_grid(const DeviceState &st, uint64_t n) {
     return static_cast<int>(std::max<uint64_t>(1, std::min(want, cap)));
 }
 
-// Digest of n words at d_words; allocates its scratch for the call and synchronises the stream.
+// The per-device scratch of the digest and verify kernels: [DigestScratch + partials][mismatch counter]. Allocated at the
+// first use on the device and kept (gpuprobe_shutdown frees it), so that neither the 50,000-element drop-in probe nor a
+// digest inside a timed pass pays a cudaMalloc/cudaFree pair (both take device-wide locks). Caller holds st.scratch_mu.
+constexpr size_t VERIFY_COUNTER_OFFSET = (DIGEST_SCRATCH_BYTES + 15) & ~static_cast<size_t>(15);
+constexpr size_t DEVICE_SCRATCH_BYTES = VERIFY_COUNTER_OFFSET + 16;
+
+static int ensure_scratch(DeviceState &st, char *err, size_t errlen) {
+    if (st.scratch) return GPUPROBE_OK;
+    GP_CUDA(cudaMalloc(&st.scratch, DEVICE_SCRATCH_BYTES));
+    return GPUPROBE_OK;
+}
+
+// Digest of n words at d_words; uses the device's cached scratch and synchronises the stream.
 int run_digest(DeviceState &st, const void *d_words, uint64_t n, uint64_t *sum64, uint32_t *xor32,
                       cudaStream_t stream, char *err, size_t errlen) {
     if (n == 0) {
@@ -562,39 +582,38 @@ int run_digest(DeviceState &st, const void *d_words, uint64_t n, uint64_t *sum64
         *xor32 = 0;
         return GPUPROBE_OK;
     }
-    DigestScratch *scr = nullptr;
-    GP_CUDA(cudaMalloc(&scr, DIGEST_SCRATCH_BYTES));
-    int rc = GPUPROBE_OK;
+    std::lock_guard<std::mutex> lock(st.scratch_mu);
+    int rc = ensure_scratch(st, err, errlen);
+    if (rc) return rc;
+    DigestScratch *scr = static_cast<DigestScratch *>(st.scratch);
     DigestScratch host{};
-    do {
-        cudaError_t e = cudaMemsetAsync(scr, 0, sizeof(DigestScratch), stream);
-        if (e == cudaSuccess) {
-            const int vec_ok = (reinterpret_cast<uintptr_t>(d_words) & 15u) == 0;
-            digest_kernel<<<digest_grid(st, n), 256, 0, stream>>>(static_cast<const uint32_t *>(d_words), n, vec_ok, scr);
-            e = cudaGetLastError();
-        }
-        if (e == cudaSuccess) e = cudaMemcpyAsync(&host, scr, sizeof(DigestScratch), cudaMemcpyDeviceToHost, stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
-        if (e != cudaSuccess) {
-            set_err(err, errlen, "digest failed: %s", cudaGetErrorString(e));
-            (void)cudaGetLastError();
-            rc = GPUPROBE_ECUDA;
-        }
-    } while (0);
-    cudaFree(scr);
-    if (rc == GPUPROBE_OK) {
-        *sum64 = host.out_sum;
-        *xor32 = host.out_xor;
+    // result words and ticket start at zero (a kernel that died mid-way may have left a stale ticket)
+    cudaError_t e = cudaMemsetAsync(scr, 0, sizeof(DigestScratch), stream);
+    if (e == cudaSuccess) {
+        const int vec_ok = (reinterpret_cast<uintptr_t>(d_words) & 15u) == 0;
+        digest_kernel<<<digest_grid(st, n), 256, 0, stream>>>(static_cast<const uint32_t *>(d_words), n, vec_ok, scr);
+        e = cudaGetLastError();
     }
-    return rc;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&host, scr, sizeof(DigestScratch), cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    if (e != cudaSuccess) {
+        set_err(err, errlen, "digest failed: %s", cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        return GPUPROBE_ECUDA;
+    }
+    *sum64 = host.out_sum;
+    *xor32 = host.out_xor;
+    return GPUPROBE_OK;
 }
 
 static int run_verify(DeviceState &st, const float *d_c, uint64_t first, uint64_t n, uint32_t seed, int kind,
                       uint64_t *mismatches, cudaStream_t stream, char *err, size_t errlen) {
     *mismatches = 0;
     if (n == 0) return GPUPROBE_OK;
-    unsigned long long *d_bad = nullptr;
-    GP_CUDA(cudaMalloc(&d_bad, sizeof(unsigned long long)));
+    std::lock_guard<std::mutex> lock(st.scratch_mu);
+    int rc = ensure_scratch(st, err, errlen);
+    if (rc) return rc;
+    unsigned long long *d_bad = reinterpret_cast<unsigned long long *>(static_cast<unsigned char *>(st.scratch) + VERIFY_COUNTER_OFFSET);
     unsigned long long h_bad = 0;
     cudaError_t e = cudaMemsetAsync(d_bad, 0, sizeof(unsigned long long), stream);
     if (e == cudaSuccess) {
@@ -604,7 +623,6 @@ static int run_verify(DeviceState &st, const float *d_c, uint64_t first, uint64_
     }
     if (e == cudaSuccess) e = cudaMemcpyAsync(&h_bad, d_bad, sizeof(h_bad), cudaMemcpyDeviceToHost, stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
-    cudaFree(d_bad);
     if (e != cudaSuccess) {
         set_err(err, errlen, "verify failed: %s", cudaGetErrorString(e));
         (void)cudaGetLastError();
@@ -789,14 +807,38 @@ extern "C" int gpuprobe_vectoradd(const gpuprobe_vadd_cfg *cfg, gpuprobe_vadd_re
 namespace gp {
 constexpr uint64_t BUF_CHUNK_ELEMS = 8ull << 20;  // default: 32 MiB per array per chunk
 constexpr int BUF_SLOTS = 3;                      // default number of chunks in flight
-constexpr int BUF_MAX_SLOTS = 4;                  // = number of copy streams per device
 
-struct BufSlot {
-    float *d_a = nullptr, *d_b = nullptr, *d_c = nullptr;
-    float *h_a = nullptr, *h_b = nullptr, *h_c = nullptr;  // pinned bounce (pageable callers only)
-    cudaEvent_t done = nullptr;
-    uint64_t pending_off = 0, pending_n = 0;  // chunk whose C still sits in h_c
-};
+// Makes slot `sl` able to stage `chunk` elements (and to bounce them through pinned memory when `bounce`). The buffers
+// are cached in DeviceState and only ever grow: the drop-in vectorAdd (50,000 elements, the reference's one real
+// workload) and a validator that re-probes periodically pay the allocations once per process, not per call.
+static cudaError_t ensure_slot(BufSlot &sl, uint64_t chunk, bool bounce) {
+    cudaError_t e = cudaSuccess;
+    if (!sl.done && (e = cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming)) != cudaSuccess) return e;
+    if (sl.dev_cap < chunk) {
+        cudaFree(sl.d_a);
+        cudaFree(sl.d_b);
+        cudaFree(sl.d_c);
+        sl.d_a = sl.d_b = sl.d_c = nullptr;
+        sl.dev_cap = 0;
+        if ((e = cudaMalloc(&sl.d_a, chunk * sizeof(float))) != cudaSuccess) return e;
+        if ((e = cudaMalloc(&sl.d_b, chunk * sizeof(float))) != cudaSuccess) return e;
+        if ((e = cudaMalloc(&sl.d_c, chunk * sizeof(float))) != cudaSuccess) return e;
+        sl.dev_cap = chunk;
+    }
+    if (bounce && sl.host_cap < chunk) {
+        if (sl.h_a) cudaFreeHost(sl.h_a);
+        if (sl.h_b) cudaFreeHost(sl.h_b);
+        if (sl.h_c) cudaFreeHost(sl.h_c);
+        sl.h_a = sl.h_b = sl.h_c = nullptr;
+        sl.host_cap = 0;
+        if ((e = cudaHostAlloc(&sl.h_a, chunk * sizeof(float), cudaHostAllocDefault)) != cudaSuccess) return e;
+        if ((e = cudaHostAlloc(&sl.h_b, chunk * sizeof(float), cudaHostAllocDefault)) != cudaSuccess) return e;
+        if ((e = cudaHostAlloc(&sl.h_c, chunk * sizeof(float), cudaHostAllocDefault)) != cudaSuccess) return e;
+        sl.host_cap = chunk;
+    }
+    sl.pending_off = sl.pending_n = 0;
+    return cudaSuccess;
+}
 
 static bool is_pinned(const void *p) {
     cudaPointerAttributes at{};
@@ -854,18 +896,9 @@ extern "C" int gpuprobe_vectoradd_buffers(int dev, const float *a, const float *
     if (const char *e = getenv("GPUPROBE_BUF_SLOTS")) max_slots = std::max(1, std::min(BUF_MAX_SLOTS, atoi(e)));
     const uint64_t chunk = std::min<uint64_t>(n, chunk_elems);
     const int slots = static_cast<int>(std::min<uint64_t>(static_cast<uint64_t>(max_slots), (n + chunk - 1) / chunk));
-    BufSlot slot[BUF_MAX_SLOTS];
-    auto cleanup = [&]() {
-        for (int s = 0; s < BUF_MAX_SLOTS; ++s) {
-            cudaFree(slot[s].d_a);
-            cudaFree(slot[s].d_b);
-            cudaFree(slot[s].d_c);
-            if (slot[s].h_a) cudaFreeHost(slot[s].h_a);
-            if (slot[s].h_b) cudaFreeHost(slot[s].h_b);
-            if (slot[s].h_c) cudaFreeHost(slot[s].h_c);
-            if (slot[s].done) cudaEventDestroy(slot[s].done);
-        }
-    };
+    BufSlot *slot = st.buf_slots;  // cached staging, guarded by st.mu (held)
+    // After a failure the cache is dropped: whatever state the slots were in, the next call starts from nothing.
+    auto cleanup = [&]() { free_buf_slots(st); };
 #define GP_TRY(call)                                                                                   \
     do {                                                                                               \
         cudaError_t e_ = (call);                                                                       \
@@ -878,17 +911,7 @@ extern "C" int gpuprobe_vectoradd_buffers(int dev, const float *a, const float *
         }                                                                                              \
     } while (0)
 
-    for (int s = 0; s < slots; ++s) {
-        GP_TRY(cudaMalloc(&slot[s].d_a, chunk * sizeof(float)));
-        GP_TRY(cudaMalloc(&slot[s].d_b, chunk * sizeof(float)));
-        GP_TRY(cudaMalloc(&slot[s].d_c, chunk * sizeof(float)));
-        GP_TRY(cudaEventCreateWithFlags(&slot[s].done, cudaEventDisableTiming));
-        if (!direct) {
-            GP_TRY(cudaHostAlloc(&slot[s].h_a, chunk * sizeof(float), cudaHostAllocDefault));
-            GP_TRY(cudaHostAlloc(&slot[s].h_b, chunk * sizeof(float), cudaHostAllocDefault));
-            GP_TRY(cudaHostAlloc(&slot[s].h_c, chunk * sizeof(float), cudaHostAllocDefault));
-        }
-    }
+    for (int s = 0; s < slots; ++s) GP_TRY(ensure_slot(slot[s], chunk, !direct));
 
     uint64_t off = 0;
     for (uint64_t k = 0; off < n; ++k, off += chunk) {
@@ -930,7 +953,8 @@ extern "C" int gpuprobe_vectoradd_buffers(int dev, const float *a, const float *
         for (int s = 0; s < slots; ++s)
             if (slot[s].pending_n) std::memcpy(c + slot[s].pending_off, slot[s].h_c, slot[s].pending_n * sizeof(float));
     }
-    cleanup();
+    // GPUPROBE_BUF_CACHE=0: give the staging back after every call (callers that probe once and then run something else)
+    if (const char *e = getenv("GPUPROBE_BUF_CACHE"); e && *e == '0') cleanup();
     return GPUPROBE_OK;
 #undef GP_TRY
 }

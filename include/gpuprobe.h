@@ -17,9 +17,15 @@
  *   `err` (may be NULL) receives a NUL-terminated message of at most errlen bytes.
  *   Nothing is thrown across the ABI and there are no callbacks.  The caller owns every
  *   struct and buffer it passes.  Unless an entry point says otherwise the library
- *   allocates the device memory it needs and frees it before returning.  Every entry
- *   point selects its device itself (safe from any OS thread, e.g. a Go goroutine that
- *   migrated); calls that use the same device are serialised inside the library.
+ *   allocates the device memory it needs: the probes' arrays are freed before the call
+ *   returns; two small caches live per device until gpuprobe_shutdown() -- the digest /
+ *   verify scratch (about 14 KiB) and the staging slots of gpuprobe_vectoradd_buffers
+ *   (as large as the largest chunk staged so far; env GPUPROBE_BUF_CACHE=0 frees them after
+ *   every call).  Every entry point selects its device itself (safe from any OS thread,
+ *   e.g. a Go goroutine that migrated).  The synchronous probes (gpuprobe_vectoradd,
+ *   _vectoradd_buffers, _p2p_matrix, _allreduce_*) are serialised per device inside the
+ *   library; the *_device entry points only enqueue work on the caller's stream and
+ *   take no probe lock (digest and verify serialise on their shared scratch).
  *   There is no CPU fallback: without a usable sm_100 device the compute entry points
  *   return GPUPROBE_ENODEV / GPUPROBE_EARCH.
  */
@@ -221,8 +227,8 @@ GPUPROBE_API int gpuprobe_fill_inputs_device(int dev, float *d_a, float *d_b, ui
                                 int gen_kind, void *stream, char *err, size_t errlen);
 
 /* sum64 / xor32 of the bit patterns of a device array of n 32-bit words; synchronises
- * `stream` before returning.  Uses a small device scratch buffer that the library
- * allocates for the call. */
+ * `stream` before returning.  Uses the device's cached scratch buffer (allocated at the
+ * first digest or verify on that device, freed by gpuprobe_shutdown). */
 GPUPROBE_API int gpuprobe_digest_device(int dev, const void *d_words, uint64_t n, uint64_t *sum64, uint32_t *xor32,
                            void *stream, char *err, size_t errlen);
 
@@ -238,7 +244,10 @@ GPUPROBE_API int gpuprobe_digest_device(int dev, const void *d_words, uint64_t n
  * `stream`, launches, copies the 16-byte result back and synchronises `stream`.  All calls on
  * a device share the array: the library serialises them, and work that reads the array must
  * not overlap on the GPU.  The first call on each device looks the array's address up (set-up);
- * make that first call outside any stream capture. */
+ * make that first call outside any stream capture.  With CUDA's default lazy module loading that
+ * look-up may also be what loads the library's device code onto the GPU, and the array is reserved
+ * at that moment -- so "allocates nothing" holds from the second call on: make the set-up call at
+ * start-up (n = 0 is enough), before the GPU fills up, not when memory is already exhausted. */
 #define GPUPROBE_NOALLOC_MAX_WORDS (1ull << 30)
 #define GPUPROBE_NOALLOC_SCRATCH_BYTES 196864
 GPUPROBE_API int gpuprobe_digest_device_noalloc(int dev, const void *d_words, uint64_t n, uint64_t *sum64,
@@ -305,7 +314,8 @@ GPUPROBE_API int gpuprobe_allreduce_i32_push(const gpuprobe_ar_cfg *cfg, gpuprob
  * the two-shot kernel when NVLink multicast is unavailable.  out->impl says which ran.  No reference counterpart. */
 GPUPROBE_API int gpuprobe_allreduce_i32_auto(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
 
-/* Releases cached per-device state (streams, events, scratch).  Optional. */
+/* Releases cached per-device state: streams, the digest/verify scratch, the staging slots and pinned
+ * bounce buffers of gpuprobe_vectoradd_buffers.  Optional; the library re-creates them on demand. */
 GPUPROBE_API void gpuprobe_shutdown(void);
 
 #ifdef __cplusplus

@@ -40,6 +40,12 @@ def test_noalloc_digest_matches_allocating_digest_twice_in_a_row(gp, torch_cuda)
     want2 = gp.digest_device(w2, n2, stream=stream)
     assert want1 != want2
 
+    # the checker's own answer, computed on the CPU from the same words
+    from oracle import oracle as oc
+
+    host1 = w1.cpu().numpy().view(np.float32)
+    assert want1 == oc.digest(host1)
+
     got1 = gp.digest_device_noalloc(w1, n1, stream=stream)  # first call on this device: does the set-up
     got2 = gp.digest_device_noalloc(w2, n2, stream=stream)  # second call re-uses the same scratch array
     assert got1 == want1
