@@ -794,7 +794,7 @@ extern "C" int gpuprobe_allreduce_i32_auto(const gpuprobe_ar_cfg *cfg, gpuprobe_
     }
     const int nd = cfg->ndev;
     if (nd != 2 && nd != 4 && nd != 8) return allreduce_symmetric(cfg, out, 0, err, errlen);  // any rank count: NVLS only
-    int algo = nd == 2 ? 1 : 2;
+    int algo = nd == 2 ? 3 : 2;  // 2 ranks: all-push two-shot (646 vs 626 GB/s for pull+push); 4 and 8: hybrid (684 / 815)
     if (const char *e = getenv("GPUPROBE_AR_AUTO_ALGO")) algo = std::max(0, std::min(3, atoi(e)));
     int rc = allreduce_symmetric(cfg, out, algo, err, errlen);
     if (rc == GPUPROBE_ENOPEER && algo != 1) rc = allreduce_symmetric(cfg, out, 1, err, errlen);  // no multicast on this box

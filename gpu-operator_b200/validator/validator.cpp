@@ -286,24 +286,55 @@ std::vector<std::string> parseFlowList(const std::string &v) {
 }
 }  // namespace
 
+// Cuts a trailing comment: '#' opens one only at the start of the line or after white space, and never inside quotes.
+static std::string stripComment(const std::string &line) {
+    char quote = 0;
+    for (size_t i = 0; i < line.size(); ++i) {
+        const char ch = line[i];
+        if (quote) {
+            if (ch == quote) quote = 0;
+        } else if (ch == '"' || ch == '\'') {
+            quote = ch;
+        } else if (ch == '#' && (i == 0 || line[i - 1] == ' ' || line[i - 1] == '\t')) {
+            return line.substr(0, i);
+        }
+    }
+    return line;
+}
+
 // A line-oriented reader for the block-style subset of YAML that the workload manifests use
 // (validator/cuda-workload-validation.yaml, validator/plugin-workload-validation.yaml):
-// nested maps by indentation, "- " sequences of maps, flow lists for command/args.
+// nested maps by indentation, "- " sequences of maps, flow lists for command/args. What it cannot
+// read it refuses by name (see validator.hpp) instead of silently dropping.
 std::string loadPodSpec(const std::string &path, PodSpec *pod) {
     std::ifstream in(path);
     if (!in) return sprintfStr("open %s: %s", path.c_str(), strerror(errno));
     std::string line, kind;
     std::string section;      // "initContainers" / "containers" / ""
-    std::string sub;          // "env" / "limits" / "labels" / "metadata" ...
-    std::string pendingEnvName;
+    std::string sub;          // "env" / "limits" / "labels" / "volumeMounts" / "volumes" ...
+    int subIndent = -1;       // indentation of the key that opened `sub`
+    std::string pendingEnvName, pendingMountName, pendingVolumeName;
     int sectionIndent = -1;
     std::vector<std::string> *listTarget = nullptr;  // command:/args: given as a block sequence on the next lines
     int listIndent = 0;
+    int lineNo = 0;
+    bool sawContent = false;
+    auto unsupported = [&](const char *what) {
+        return sprintfStr("%s:%d: %s is not supported by the validator's manifest reader (it reads plain block-style maps, "
+                          "\"- \" sequences and flow lists only)", path.c_str(), lineNo, what);
+    };
     while (std::getline(in, line)) {
-        size_t hash = line.find(" #");
-        if (hash != std::string::npos) line = line.substr(0, hash);
-        if (trim(line).empty() || trim(line)[0] == '#') continue;
-        int indent = static_cast<int>(line.find_first_not_of(' '));
+        ++lineNo;
+        line = stripComment(line);
+        if (trim(line).empty()) continue;
+        if (trim(line) == "---") {
+            if (sawContent) return unsupported("a second YAML document (\"---\")");
+            continue;
+        }
+        sawContent = true;
+        const size_t firstNonSpace = line.find_first_not_of(' ');
+        if (firstNonSpace != std::string::npos && line[firstNonSpace] == '\t') return unsupported("tab indentation");
+        int indent = static_cast<int>(firstNonSpace);
         std::string t = trim(line);
         bool dash = t.rfind("- ", 0) == 0;
         if (dash) t = trim(t.substr(2));
@@ -316,10 +347,23 @@ std::string loadPodSpec(const std::string &path, PodSpec *pod) {
         size_t colon = t.find(':');
         if (colon == std::string::npos) continue;
         std::string key = unquote(t.substr(0, colon)), val = trim(t.substr(colon + 1));
+        if (key == "<<") return unsupported("a merge key (\"<<\")");
+        if (!val.empty()) {
+            if (val[0] == '&') return unsupported("an anchor (\"&name\")");
+            if (val[0] == '*') return unsupported("an alias (\"*name\")");
+            if (val[0] == '{') return unsupported("a flow mapping (\"{...}\")");
+            if (val[0] == '|' || val[0] == '>') return unsupported("a block scalar (\"|\" or \">\")");
+        }
+        // a line at or left of the key that opened the current sub-map closes it (a "- " item may sit at the key's indent)
+        if (!sub.empty() && subIndent >= 0 && (indent < subIndent || (indent == subIndent && !dash))) {
+            sub.clear();
+            subIndent = -1;
+        }
 
         if (indent == 0) {
             section.clear();
             sub = key;
+            subIndent = -1;
             if (key == "kind") kind = unquote(val);
             continue;
         }
@@ -331,20 +375,27 @@ std::string loadPodSpec(const std::string &path, PodSpec *pod) {
         }
         if (!section.empty() && indent <= sectionIndent && !dash) section.clear();
         if (section.empty()) {
-            if (key == "labels" || key == "tolerations") sub = key;
-            else if (key == "app" && sub == "labels") pod->appLabel = unquote(val);
+            if (key == "labels" || key == "tolerations" || key == "volumes") {
+                sub = key;
+                subIndent = indent;
+            } else if (key == "app" && sub == "labels") pod->appLabel = unquote(val);
+            else if (sub == "volumes" && key == "name" && dash) pendingVolumeName = unquote(val);
+            else if (sub == "volumes" && key == "path" && !pendingVolumeName.empty()) pod->hostPathVolumes[pendingVolumeName] = unquote(val);
+            else if (sub == "volumes") continue;  // hostPath: / type: ...
             else if (key == "generateName") pod->generateName = unquote(val);
             else if (key == "namespace") pod->namespace_ = unquote(val);
             else if (key == "restartPolicy") pod->restartPolicy = unquote(val);
             continue;
         }
         if (section != "initContainers") continue;  // the main container only echoes success
-        if (key == "env" || key == "resources" || key == "securityContext") {
+        if (key == "env" || key == "resources" || key == "securityContext" || key == "volumeMounts") {
             sub = key;
+            subIndent = indent;
             continue;
         }
         if (key == "limits" || key == "requests") {
             sub = key;
+            subIndent = indent;
             continue;
         }
         if (sub == "env" && key == "name" && dash) {
@@ -354,6 +405,11 @@ std::string loadPodSpec(const std::string &path, PodSpec *pod) {
         if (sub == "env" && key == "value") {
             if (!pendingEnvName.empty()) pod->initEnv[pendingEnvName] = unquote(val);
             pendingEnvName.clear();
+            continue;
+        }
+        if (sub == "volumeMounts") {
+            if (key == "name") pendingMountName = unquote(val);
+            else if (key == "mountPath" && !pendingMountName.empty()) pod->initVolumeMounts[pendingMountName] = unquote(val);
             continue;
         }
         if (sub == "limits") {
@@ -377,6 +433,20 @@ std::string loadPodSpec(const std::string &path, PodSpec *pod) {
     if (kind != "Pod") return sprintfStr("no kind \"Pod\" is registered in %s (kind: %s)", path.c_str(), kind.c_str());
     if (pod->initArgs.empty()) return sprintfStr("%s: no initContainers[0].args", path.c_str());
     return "";
+}
+
+bool mountsHostDir(const PodSpec &pod, const std::string &dir) {
+    for (auto &m : pod.initVolumeMounts) {
+        auto v = pod.hostPathVolumes.find(m.first);
+        if (m.second == dir && v != pod.hostPathVolumes.end() && v->second == dir) return true;
+    }
+    return false;
+}
+
+void ensureValidationsVolume(PodSpec *pod) {
+    if (mountsHostDir(*pod, defaultStatusPath)) return;
+    pod->hostPathVolumes["run-nvidia-validations"] = defaultStatusPath;
+    pod->initVolumeMounts["run-nvidia-validations"] = defaultStatusPath;
 }
 
 // ------------------------------------------------------------------------------ node resources
@@ -466,7 +536,9 @@ private:
             envS.push_back(k + "=" + v);
         };
         for (auto &kv : pod_.initEnv) setEnv(kv.first, kv.second);
-        setEnv("OUTPUT_DIR", flags_.outputDir);
+        // The pod has its own filesystem: what it writes under /run/nvidia/validations reaches this validator's output
+        // directory only through a hostPath mount of that path. Without one the child gets a directory of its own.
+        setEnv("OUTPUT_DIR", mountsHostDir(pod_, defaultStatusPath) ? flags_.outputDir : "/nonexistent/pod-private" + flags_.outputDir);
         if (!flags_.nodeName.empty()) setEnv("NODE_NAME", flags_.nodeName);
         // a pod that was allocated one GPU by the device plugin sees one GPU
         for (auto &kv : pod_.initResourceLimits)
@@ -584,6 +656,13 @@ static std::string runWorkload(Runtime &rt, const char *specPath, const char *wh
         }
     // the plugin workload (one allocated GPU) must not overwrite the cuda workload's node-wide results
     if (!resourceName.empty()) pod.initEnv["GPUPROBE_RESULTS_BASENAME"] = "gpuprobe-plugin-results";
+    // New: the results file has to leave the pod. The reference's workload manifests declare no volumes, so the pod gets the
+    // validations hostPath here if its manifest does not already mount it (GPUPROBE_NO_VOLUME_INJECT=1: tests of the
+    // failure mode only).
+    if (!*envOr("GPUPROBE_NO_VOLUME_INJECT", "")) ensureValidationsVolume(&pod);
+    if (!mountsHostDir(pod, defaultStatusPath))
+        logInfo("warning: %s workload pod does not mount %s: its probe results will not reach the metrics exporter", what,
+                defaultStatusPath);
     std::string name;
     e = rt.launcher->create(pod, &name);
     if (!e.empty()) return sprintfStr("failed to create %s validation pod %s, err %s", what, pod.generateName.c_str(), e.c_str());

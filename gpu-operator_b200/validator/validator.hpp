@@ -87,9 +87,21 @@ struct PodSpec {
     std::vector<std::string> initArgs;     // e.g. ["vectorAdd"]
     std::map<std::string, std::string> initEnv;
     std::map<std::string, std::string> initResourceLimits;  // plugin: {resourceName: "1"}
+    std::map<std::string, std::string> initVolumeMounts;    // init container: volume name -> mountPath
+    std::map<std::string, std::string> hostPathVolumes;     // spec.volumes: volume name -> hostPath.path
 };
+// New: the workload pod must mount the validations hostPath, or the probe's results file never leaves the pod (the
+// reference's workload pods declare no volumes: validator/cuda-workload-validation.yaml:1-35). Adds the volume and the
+// init container's mount when the manifest lacks them -- what the Go forwardProbeEnv does (integration/validator/gpuprobe.go).
+void ensureValidationsVolume(PodSpec *pod);
+// True if the init container mounts a hostPath volume at `dir`.
+bool mountsHostDir(const PodSpec &pod, const std::string &dir);
 // Reads the subset of the Pod manifest the validator touches. Like the reference it treats an
 // unreadable file as fatal (the reference panics, main.go:1064-1066): returns an error string.
+// This is a reader for the block-style YAML subset the two shipped manifests use, not a YAML parser: nested maps by
+// indentation, "- " sequences of maps, flow or block lists for command/args, comments outside quotes. Anchors and
+// aliases, merge keys, flow mappings, block scalars (| and >), tabs and a second document are rejected with an error
+// that names the construct and the line.
 std::string loadPodSpec(const std::string &path, PodSpec *pod);
 
 // ---- the two seams to the Kubernetes API --------------------------------------------------

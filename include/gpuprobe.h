@@ -310,8 +310,8 @@ GPUPROBE_API int gpuprobe_allreduce_i32_hybrid(const gpuprobe_ar_cfg *cfg, gpupr
 GPUPROBE_API int gpuprobe_allreduce_i32_push(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
 
 /* The hand-written kernel the validator uses when GPUPROBE_AR_IMPL does not name one: the measured best for the
- * rank count (two-shot over peer mappings at 2 ranks, hybrid at 4 and 8; profiles/r02_fabric.md), falling back to
- * the two-shot kernel when NVLink multicast is unavailable.  out->impl says which ran.  No reference counterpart. */
+ * rank count (all-push two-shot at 2 ranks, hybrid at 4 and 8; profiles/r02_fabric.md), falling back to the
+ * pull+push two-shot kernel when NVLink multicast is unavailable.  out->impl says which ran.  No reference counterpart. */
 GPUPROBE_API int gpuprobe_allreduce_i32_auto(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
 
 /* Releases cached per-device state: streams, the digest/verify scratch, the staging slots and pinned

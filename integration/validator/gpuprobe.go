@@ -41,8 +41,13 @@ const (
 	nominalLinkGBps      = 900.0
 )
 
+const validationsVolumeName = "run-nvidia-validations"
+
 // forwardProbeEnv copies every GPUPROBE_* variable of the validator's own environment into the
-// workload pod's init container (validator.cuda.env / validator.plugin.env only reach the DaemonSet).
+// workload pod's init container (validator.cuda.env / validator.plugin.env only reach the DaemonSet),
+// and makes sure the pod can hand its results back: the workload manifests of the reference declare no
+// volumes (validator/cuda-workload-validation.yaml), so without the hostPath below gpuprobe-results.json
+// would stay inside the pod and the exporter's gauges would never get a value.
 func forwardProbeEnv(pod *v1.Pod) {
 	for _, kv := range os.Environ() {
 		if !strings.HasPrefix(kv, probeEnvPrefix) {
@@ -53,6 +58,29 @@ func forwardProbeEnv(pod *v1.Pod) {
 	}
 	pod.Spec.InitContainers[0].Env = append(pod.Spec.InitContainers[0].Env,
 		v1.EnvVar{Name: "OUTPUT_DIR", Value: outputDirFlag}, v1.EnvVar{Name: "NODE_NAME", Value: nodeNameFlag})
+	ensureValidationsVolume(pod)
+}
+
+// ensureValidationsVolume adds the validations hostPath (the one the validator DaemonSet itself mounts,
+// assets/state-operator-validation/0500_daemonset.yaml:50-51,158-162) and the init container's mount, unless the
+// manifest already has them (integration/patches/0006 adds them to both workload manifests).
+func ensureValidationsVolume(pod *v1.Pod) {
+	for _, m := range pod.Spec.InitContainers[0].VolumeMounts {
+		if m.MountPath == outputDirFlag {
+			return
+		}
+	}
+	hostPathType := v1.HostPathDirectoryOrCreate
+	haveVolume := false
+	for _, vol := range pod.Spec.Volumes {
+		haveVolume = haveVolume || vol.Name == validationsVolumeName
+	}
+	if !haveVolume {
+		pod.Spec.Volumes = append(pod.Spec.Volumes, v1.Volume{Name: validationsVolumeName,
+			VolumeSource: v1.VolumeSource{HostPath: &v1.HostPathVolumeSource{Path: outputDirFlag, Type: &hostPathType}}})
+	}
+	pod.Spec.InitContainers[0].VolumeMounts = append(pod.Spec.InitContainers[0].VolumeMounts,
+		v1.VolumeMount{Name: validationsVolumeName, MountPath: outputDirFlag})
 }
 
 func probeError(where string, rc C.int, msg *C.char) error {
@@ -99,8 +127,13 @@ type P2PEntry struct {
 
 type AllReduceEntry struct {
 	NDev       int     `json:"ndev"`
+	Impl       int     `json:"impl"` // GPUPROBE_AR_IMPL_*
 	BusBWGBps  float64 `json:"busbw_gbps"`
 	Mismatches uint64  `json:"mismatches"`
+	Rounds     uint32  `json:"rounds"`
+	Sum64      uint64  `json:"sum64"` // digest of the reduced buffer (ABI 2)
+	Xor32      uint32  `json:"xor32"`
+	RanksEqual bool    `json:"ranks_equal"`
 }
 
 // vectorAddHostCheck is the sample's own sequence at its own size, checked by a Go host loop:
@@ -129,12 +162,15 @@ func runProbes() error {
 		return fmt.Errorf("failed to find a CUDA device: %s", C.GoString(C.gpuprobe_strerror(rc)))
 	}
 	ndev := int(ndevC)
+	if v := int(C.gpuprobe_abi_version()); v != C.GPUPROBE_ABI_VERSION {
+		return fmt.Errorf("libgpuprobe ABI %d, this binary was built against %d", v, int(C.GPUPROBE_ABI_VERSION))
+	}
 	if err := vectorAddHostCheck(0, referenceNumElements); err != nil {
 		return err
 	}
 	log.Infof("vectorAdd of %d elements on device 0: bit-exact", referenceNumElements)
 
-	res := ProbeResults{Version: 1, Node: nodeNameFlag, Pass: true}
+	res := ProbeResults{Version: 2, Node: nodeNameFlag, Pass: true}
 	msg := (*C.char)(C.calloc(512, 1))
 	defer C.free(unsafe.Pointer(msg))
 	var failures []string
@@ -180,19 +216,30 @@ func runProbes() error {
 		cfg := C.gpuprobe_ar_cfg{ndev: C.int(ndev), count: C.uint64_t(count), iters: 20, warmup: 5}
 		var out C.gpuprobe_ar_result
 		rc := C.gpuprobe_allreduce_i32(&cfg, &out, msg, 512)
+		if rc == C.GPUPROBE_ENCCL && os.Getenv("GPUPROBE_AR_REQUIRE_NCCL") != "1" {
+			// the validator image ships no libnccl.so.2 unless it was built with GPUPROBE_NCCL_STATIC=1: the fabric
+			// still gets its check, by the library's own allreduce kernel
+			log.Warnf("NCCL unavailable (%s); running the library's allreduce kernel instead", C.GoString(msg))
+			rc = C.gpuprobe_allreduce_i32_auto(&cfg, &out, msg, 512)
+		}
 		if err := probeError("allreduce", rc, msg); err != nil {
 			failures = append(failures, err.Error())
 		} else if minLink > 0 && float64(out.frac_of_peak) < minLink {
 			failures = append(failures, fmt.Sprintf("allreduce busbw %.1f GB/s is below %.2f of %.0f GB/s", float64(out.busbw_gbps), minLink, nominalLinkGBps))
 		}
-		res.AllReduce = &AllReduceEntry{NDev: int(out.ndev), BusBWGBps: float64(out.busbw_gbps), Mismatches: uint64(out.mismatches)}
+		res.AllReduce = &AllReduceEntry{NDev: int(out.ndev), Impl: int(out.impl), BusBWGBps: float64(out.busbw_gbps),
+			Mismatches: uint64(out.mismatches), Rounds: uint32(out.rounds), Sum64: uint64(out.sum64), Xor32: uint32(out.xor32),
+			RanksEqual: out.ranks_equal != 0}
 	}
 
 	res.Pass = len(failures) == 0
 	if data, err := json.Marshal(res); err == nil {
 		tmp := filepath.Join(outputDirFlag, probeResultsFile+".tmp")
-		if os.WriteFile(tmp, data, 0644) == nil {
-			_ = os.Rename(tmp, filepath.Join(outputDirFlag, probeResultsFile))
+		if err := os.WriteFile(tmp, data, 0644); err != nil {
+			// the probes ran, but nobody will see their figures: say so (a missing hostPath mount is the usual cause)
+			log.Warnf("cannot write %s: %v", tmp, err)
+		} else if err := os.Rename(tmp, filepath.Join(outputDirFlag, probeResultsFile)); err != nil {
+			log.Warnf("cannot publish %s: %v", probeResultsFile, err)
 		}
 	}
 	C.gpuprobe_shutdown()

@@ -39,12 +39,14 @@ var (
 	}, []string{"node"})
 	probeARBusBW = promauto.NewGaugeVec(promcli.GaugeOpts{
 		Name: "gpu_operator_node_cuda_allreduce_busbw_gbps",
-		Help: "NCCL int32 allreduce bus bandwidth over all GPUs of the node, GB/s",
+		Help: "int32 allreduce bus bandwidth over all GPUs of the node, GB/s",
 	}, []string{"node"})
 )
 
-// watchProbeResults re-reads <OUTPUT_DIR>/gpuprobe-results.json (written by the cuda workload pod through the
-// shared /run/nvidia/validations hostPath) and republishes it.
+// watchProbeResults re-reads <OUTPUT_DIR>/gpuprobe-results.json and republishes it. The file is written by the cuda
+// workload pod; it reaches this pod because both mount the node's /run/nvidia/validations -- the exporter through
+// /run/nvidia (assets/state-node-status-exporter/0700_daemonset.yaml:49-51), the workload pod through the hostPath
+// that forwardProbeEnv / integration/patches/0006 add.
 func (nm *NodeMetrics) watchProbeResults() {
 	path := filepath.Join(outputDirFlag, probeResultsFile)
 	log.Printf("metrics: gpuprobe: watching %s", path)

@@ -139,7 +139,7 @@ def test_auto_allreduce_picks_a_kernel_and_matches_oracle(gp, ndev):
     for nd in [n for n in (2, 4, 8) if n <= ndev]:
         res = gp.allreduce_i32_auto(nd, (8 << 20) + 9, iters=2, warmup=1, seed=11)
         assert_reduced_buffer_matches_oracle(res, nd, (8 << 20) + 9, 11, 1, 2)
-        assert res.impl == (gp.AR_IMPL_P2P if nd == 2 else gp.AR_IMPL_HYBRID)
+        assert res.impl == (gp.AR_IMPL_PUSH if nd == 2 else gp.AR_IMPL_HYBRID)
 
 
 def test_two_shot_allreduce_without_multicast(gp, ndev, monkeypatch):
@@ -151,9 +151,9 @@ def test_two_shot_allreduce_without_multicast(gp, ndev, monkeypatch):
             assert_reduced_buffer_matches_oracle(res, nd, count, 9, 2, 3)
             res = gp.allreduce_i32_push(nd, count, iters=3, warmup=2, seed=9)
             assert_reduced_buffer_matches_oracle(res, nd, count, 9, 2, 3)
-            res = gp.allreduce_i32_auto(nd, count, iters=2, warmup=1, seed=9)  # falls back to the two-shot kernel
+            res = gp.allreduce_i32_auto(nd, count, iters=2, warmup=1, seed=9)  # 2 ranks: push; else falls back to two-shot
             assert_reduced_buffer_matches_oracle(res, nd, count, 9, 1, 2)
-            assert res.impl == gp.AR_IMPL_P2P
+            assert res.impl == (gp.AR_IMPL_PUSH if nd == 2 else gp.AR_IMPL_P2P)
     with pytest.raises(gp.GpuProbeError) as e:
         gp.allreduce_i32_nvls(2, 1024, iters=1, warmup=1)
     assert e.value.code == gp.ENOPEER

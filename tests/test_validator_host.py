@@ -180,6 +180,86 @@ spec:
     assert (out / "cuda-ready").exists()
 
 
+def test_manifest_comment_marker_inside_quotes_is_data(tmp_path):
+    """A '#' inside a quoted string is part of the string, not the start of a comment."""
+    marker = tmp_path / "ran"
+    d = manifests(tmp_path)
+    text = CUDA_MANIFEST.format(cmd=f"echo 'a #b' > {marker}", restart="OnFailure")
+    (tmp_path / "manifests" / "cuda-workload-validation.yaml").write_text(
+        text.replace("restartPolicy: OnFailure", "restartPolicy: OnFailure   # a real comment"))
+    out = tmp_path / "v"
+    r = run(["-c", "cuda", "-ns", "ns", "-o", str(out)], {"GPUPROBE_MANIFEST_DIR": d})
+    assert r.returncode == 0, r.stderr
+    assert marker.read_text().strip() == "a #b"
+
+
+@pytest.mark.parametrize("snippet,what", [
+    ('    args: |\n      vectorAdd\n', "a block scalar"),
+    ('    args: >-\n      vectorAdd\n', "a block scalar"),
+    ('    args: *defaultargs\n', "an alias"),
+    ('    args: &a ["true"]\n', "an anchor"),
+    ('    args: ["true"]\n    securityContext: {privileged: true}\n', "a flow mapping"),
+    ('    args: ["true"]\n    <<: *base\n', "a merge key"),
+    ('    args: ["true"]\n---\nkind: Pod\n', "a second YAML document"),
+    ('    args: ["true"]\n\tenv: []\n', "tab indentation"),
+])
+def test_manifest_constructs_the_reader_cannot_take_are_named(tmp_path, snippet, what):
+    """The mirror's loadPodSpec is a reader for the YAML subset of the two shipped manifests (the reference decodes
+    any YAML, main.go:1061-1081); what it cannot read it refuses with the construct and the line, never silently."""
+    d = tmp_path / "manifests"
+    d.mkdir()
+    (d / "cuda-workload-validation.yaml").write_text(
+        "kind: Pod\nmetadata:\n  generateName: x-\nspec:\n  restartPolicy: Never\n  initContainers:\n  - name: cuda-validation\n" + snippet)
+    r = run(["-c", "cuda", "-ns", "ns", "-o", str(tmp_path / "v")], {"GPUPROBE_MANIFEST_DIR": str(d)})
+    assert r.returncode == 1
+    last = r.stderr.strip().splitlines()[-1]
+    assert what in last and "is not supported by the validator's manifest reader" in last
+    assert "cuda-workload-validation.yaml:" in last  # path:line
+
+
+VOLUMES = """    volumeMounts:
+      - name: run-nvidia-validations
+        mountPath: /run/nvidia/validations
+  volumes:
+    - name: run-nvidia-validations
+      hostPath:
+        path: /run/nvidia/validations
+        type: DirectoryOrCreate
+"""
+
+
+@pytest.mark.parametrize("mounted,inject", [(True, False), (False, True), (False, False)])
+def test_probe_results_leave_the_pod_only_through_the_validations_mount(tmp_path, mounted, inject):
+    """The results file is written inside the workload pod; the metrics exporter reads it from the node's
+    /run/nvidia/validations. It gets there only if the pod mounts that hostPath (the reference's workload pods declare
+    no volumes at all, validator/cuda-workload-validation.yaml:1-35). Three cases: the manifest mounts it; it does not
+    and the validator adds the mount (what forwardProbeEnv does in the Go patch); neither -- validation still passes,
+    but loudly without results."""
+    d = tmp_path / "manifests"
+    d.mkdir()
+    text = CUDA_MANIFEST.format(cmd="echo pass-true > $OUTPUT_DIR/gpuprobe-results.json || echo cannot write results >&2", restart="Never")
+    (d / "cuda-workload-validation.yaml").write_text(text + (VOLUMES if mounted else ""))
+    out = tmp_path / "v"
+    env = {"GPUPROBE_MANIFEST_DIR": str(d)}
+    if not inject:
+        env["GPUPROBE_NO_VOLUME_INJECT"] = "1"
+    r = run(["-c", "cuda", "-ns", "ns", "-o", str(out)], env)
+    assert r.returncode == 0, r.stderr
+    assert (out / "cuda-ready").exists()
+    if mounted or inject:
+        assert (out / "gpuprobe-results.json").read_text().strip() == "pass-true"
+        assert "does not mount" not in r.stderr
+    else:
+        assert not (out / "gpuprobe-results.json").exists()
+        assert "cuda workload pod does not mount /run/nvidia/validations" in r.stderr
+
+
+def test_shipped_headless_manifests_mount_the_validations_dir():
+    for f in ("cuda-workload-validation.yaml", "plugin-workload-validation.yaml"):
+        text = open(os.path.join(ROOT, "gpu-operator_b200", "validator", "manifests", f)).read()
+        assert "mountPath: /run/nvidia/validations" in text and "path: /run/nvidia/validations" in text
+
+
 def test_missing_manifest_is_an_error(tmp_path):
     r = run(["-c", "cuda", "-ns", "ns", "-o", str(tmp_path / "v")], {"GPUPROBE_MANIFEST_DIR": str(tmp_path / "nowhere")})
     assert r.returncode == 1 and "error validating cuda workload: open " in r.stderr

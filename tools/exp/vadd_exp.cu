@@ -198,6 +198,90 @@ __global__ void __launch_bounds__(T) k_vadd_bulkstore(const float *__restrict__ 
     }
 }
 
+
+// ---- round 2: DRAM read/write turnaround experiments -----------------------------------------------------
+__device__ __forceinline__ unsigned long long gtimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+// Chip-wide temporal separation of reads and writes: persistent CTAs, each round pulls STAGES tiles of A and of B into
+// shared memory with bulk loads, adds in place, and sends the STAGES result tiles back with bulk stores. With period_ns > 0
+// the issuing thread only starts loads while (globaltimer % period_ns) < read_ns and only starts stores in the rest of
+// the period, so every SM of the chip reads in the same window and writes in the same window. period_ns = 0: same
+// structure, no windows (the control).
+template <int TILE_F, int STAGES, int T>
+__global__ void __launch_bounds__(T) k_vadd_phased(const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ c, size_t n_tiles,
+                                                   unsigned period_ns, unsigned read_ns) {
+    extern __shared__ __align__(128) unsigned char sm[];
+    constexpr uint32_t TILE_B = TILE_F * 4u;
+    float *sa = (float *)sm, *sb = (float *)(sm + (size_t)STAGES * TILE_B);
+    uint64_t *full = (uint64_t *)(sm + 2 * (size_t)STAGES * TILE_B);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) mb_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const size_t n_groups = n_tiles / STAGES;  // n_tiles is a multiple of STAGES in this harness
+    uint32_t round = 0;
+    for (size_t g = blockIdx.x; g < n_groups; g += gridDim.x, ++round) {
+        const size_t t0 = g * STAGES;
+        if (threadIdx.x == 0) {
+            if (period_ns) while ((unsigned)(gtimer_ns() % period_ns) >= read_ns) {}
+            for (int s = 0; s < STAGES; ++s) {
+                mb_expect(&full[s], 2 * TILE_B);
+                g2s(sa + (size_t)s * TILE_F, a + (t0 + s) * TILE_F, TILE_B, &full[s]);
+                g2s(sb + (size_t)s * TILE_F, b + (t0 + s) * TILE_F, TILE_B, &full[s]);
+            }
+        }
+        for (int s = 0; s < STAGES; ++s) {
+            mb_wait(&full[s], round & 1);
+            float4 *pa = (float4 *)(sa + (size_t)s * TILE_F);
+            const float4 *pb = (const float4 *)(sb + (size_t)s * TILE_F);
+#pragma unroll
+            for (int i = threadIdx.x; i < TILE_F / 4; i += T) pa[i] = add4(pa[i], pb[i]);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            if (period_ns) while ((unsigned)(gtimer_ns() % period_ns) < read_ns) {}
+            for (int s = 0; s < STAGES; ++s) s2g(c + (t0 + s) * TILE_F, sa + (size_t)s * TILE_F, TILE_B);
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+// Tile order: does DRAM page locality between co-resident CTAs matter? CTA i handles tile perm(i), where perm
+// bit-reverses the low WBITS bits of i (a scatter inside windows of 2^WBITS tiles); WBITS = 0 is the identity.
+template <int T, int WBITS>
+__global__ void __launch_bounds__(T) k_vadd_swz(const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ c) {
+    unsigned i = blockIdx.x;
+    if constexpr (WBITS > 0) {
+        const unsigned low = i & ((1u << WBITS) - 1u);
+        i = (i & ~((1u << WBITS) - 1u)) | (__brev(low) >> (32 - WBITS));
+    }
+    const size_t base = (size_t)i * (T * 4) + threadIdx.x * 4;
+    float4 x = ld4<L_NC_NA>(a + base), y = ld4<L_NC_NA>(b + base);
+    st4<S_NA>(c + base, add4(x, y));
+}
+// Same 12 B/element, but each CTA first reads a whole run of RUN tiles (A and B back to back, registers), then
+// writes the RUN results: per-CTA separation of a read burst from a write burst, without shared memory.
+template <int T, int RUN>
+__global__ void __launch_bounds__(T) k_vadd_burst(const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ c) {
+    const size_t base = (size_t)blockIdx.x * (T * 4 * RUN) + threadIdx.x * 4;
+    float4 x[RUN], y[RUN];
+#pragma unroll
+    for (int r = 0; r < RUN; ++r) x[r] = ld4<L_NC_NA>(a + base + (size_t)r * T * 4);
+#pragma unroll
+    for (int r = 0; r < RUN; ++r) y[r] = ld4<L_NC_NA>(b + base + (size_t)r * T * 4);
+#pragma unroll
+    for (int r = 0; r < RUN; ++r) x[r] = add4(x[r], y[r]);
+#pragma unroll
+    for (int r = 0; r < RUN; ++r) st4<S_NA>(c + base + (size_t)r * T * 4, x[r]);
+}
+
 struct Exp { std::string name; double bytes_per_elem; std::function<void(const float *, const float *, float *, size_t, cudaStream_t)> run; };
 
 template <int T, int U, int LH, int SH> Exp mk(const char *name) {
@@ -286,6 +370,31 @@ int main(int argc, char **argv) {
     }
     for (int k : {1, 2, 4, 8, 16})
         E.push_back({"chunked_x" + std::to_string(k), 12, [k, sms](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd_chunked<256, 2><<<sms * k, 256, 0, s>>>(a, b, c, n / 2048); }});
+
+    // round 2: read/write phase separation and tile order
+    {
+        auto add_phased = [&](const char *name, auto kern, int tile_f, int stages, int ctas, unsigned period, unsigned readns) {
+            size_t smem = 2 * (size_t)stages * tile_f * 4 + stages * 8;
+            CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            E.push_back({name, 12, [=](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { kern<<<sms * ctas, 256, smem, s>>>(a, b, c, n / tile_f, period, readns); }});
+        };
+        add_phased("phased_16k_s4_x1_nowin", k_vadd_phased<4096, 4, 256>, 4096, 4, 1, 0, 0);
+        add_phased("phased_16k_s4_x1_p4us", k_vadd_phased<4096, 4, 256>, 4096, 4, 1, 4096, 2731);
+        add_phased("phased_16k_s4_x1_p8us", k_vadd_phased<4096, 4, 256>, 4096, 4, 1, 8192, 5461);
+        add_phased("phased_16k_s4_x1_p16us", k_vadd_phased<4096, 4, 256>, 4096, 4, 1, 16384, 10923);
+        add_phased("phased_16k_s6_x1_nowin", k_vadd_phased<4096, 6, 256>, 4096, 6, 1, 0, 0);
+        add_phased("phased_16k_s6_x1_p8us", k_vadd_phased<4096, 6, 256>, 4096, 6, 1, 8192, 5461);
+        add_phased("phased_8k_s4_x3_nowin", k_vadd_phased<2048, 4, 256>, 2048, 4, 3, 0, 0);
+        add_phased("phased_8k_s4_x3_p4us", k_vadd_phased<2048, 4, 256>, 2048, 4, 3, 4096, 2731);
+        add_phased("phased_8k_s4_x3_p8us", k_vadd_phased<2048, 4, 256>, 2048, 4, 3, 8192, 5461);
+        add_phased("phased_8k_s4_x3_p32us", k_vadd_phased<2048, 4, 256>, 2048, 4, 3, 32768, 21845);
+        add_phased("phased_4k_s4_x6_nowin", k_vadd_phased<1024, 4, 256>, 1024, 4, 6, 0, 0);
+        add_phased("phased_4k_s4_x6_p8us", k_vadd_phased<1024, 4, 256>, 1024, 4, 6, 8192, 5461);
+    }
+#define SWZ(W) E.push_back({"swz_brev" #W, 12, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd_swz<256, W><<<(unsigned)(n / 1024), 256, 0, s>>>(a, b, c); }})
+    SWZ(0); SWZ(4); SWZ(8); SWZ(12); SWZ(16); SWZ(20);
+#define BURST(R) E.push_back({"burst_run" #R, 12, [](const float *a, const float *b, float *c, size_t n, cudaStream_t s) { k_vadd_burst<256, R><<<(unsigned)(n / (1024 * R)), 256, 0, s>>>(a, b, c); }})
+    BURST(1); BURST(2); BURST(4); BURST(8); BURST(16);
 
     // base-pointer offsets between the three arrays (bytes)
     struct Off { const char *name; size_t a, b, c; };
