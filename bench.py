@@ -202,7 +202,7 @@ def cpu_host_loop_gbps(steps: int, warmup: int, sample_log2: int, min_seconds: f
             "n": n, "verified": bool(check), "gbps_1thread": BYTES_PER_ELEM * n / min(t1) / 1e9}
 
 
-def run_reference(args, rank: int) -> int:
+def run_reference(args, rank: int, emit) -> int:
     if rank != 0:
         return 0
     r = cpu_host_loop_gbps(args.steps, args.warmup, CPU_SAMPLE_LOG2)
@@ -220,7 +220,7 @@ def run_reference(args, rank: int) -> int:
         "note": "the reference's arithmetic for this path is a prebuilt third-party binary + Go host code, neither "
                 "buildable here; this is the oracle's C port of the host loop on all host cores",
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -370,9 +370,17 @@ def main() -> int:
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     exit_code = 0
+    # stdout carries exactly ONE line, the JSON: everything else anybody prints while this runs -- NCCL's version banner
+    # (written to fd 1 from C), child processes of the full pass -- is sent to stderr
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(obj) -> None:
+        os.write(json_fd, (json.dumps(obj) + "\n").encode())
 
     if args.impl == "reference":
-        return run_reference(args, rank)
+        return run_reference(args, rank, emit)
 
     if args.warmup < 3:
         args.warmup = 3  # timing rule: at least 3 warm-up steps
@@ -472,8 +480,8 @@ def main() -> int:
     if args.skip_e2e:
         if rank == 0:
             used = gp.vectoradd(1 << 16, dev=dev, iters=1, warmup=0, variant=args.variant, verify=0).variant
-            print(json.dumps({"experiment": True, "variant": gp.VARIANT_NAMES[used], "value": round(value, 1),
-                              "ms_per_step": round(ms_max / args.steps, 5), "steps": args.steps, "clocks": clocks}), flush=True)
+            emit({"experiment": True, "variant": gp.VARIANT_NAMES[used], "value": round(value, 1),
+                  "ms_per_step": round(ms_max / args.steps, 5), "steps": args.steps, "clocks": clocks})
         if distributed:
             dist.destroy_process_group()
         return 0
@@ -596,7 +604,7 @@ def main() -> int:
             dist.barrier(group=gloo)
 
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if distributed:
         dist.destroy_process_group()
     return exit_code  # non-zero when a fabric probe failed or disagreed with the oracle: the line above says which

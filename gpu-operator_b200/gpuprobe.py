@@ -13,7 +13,9 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libgpuprobe.so")
+# GPUPROBE_LIB selects another build of the same library (e.g. lib/libgpuprobe_ncclstatic.so, the variant the validator
+# image ships); the default is the in-tree build.
+LIB_PATH = os.environ.get("GPUPROBE_LIB") or os.path.join(HERE, "lib", "libgpuprobe.so")
 HEADER_PATH = os.path.join(os.path.dirname(HERE), "include", "gpuprobe.h")
 
 ABI_VERSION = 2

@@ -19,6 +19,7 @@
 #include <cstring>
 #include <ctime>
 #include <fstream>
+#include <mutex>
 #include <random>
 #include <sstream>
 #include <thread>
@@ -752,27 +753,39 @@ static std::string runCommandMaybeWait(const Runtime &rt, const std::vector<std:
     }
 }
 
+// Driver.runValidation (main.go:609-628): getDriverRoot (:585-593) -- a pre-installed host driver is seen at /host, else
+// the driver container's root /run/nvidia/driver; for a driver container first assertDriverContainerReady (:598-607:
+// `stat /run/nvidia/validations/.driver-ctr-ready`), then `chroot <root> nvidia-smi`.
+// GPUPROBE_HEADLESS=1 (tools/full_pass.py, the GPU tests) adds what the reference does not have: on a box with
+// neither mount the driver in the current root is checked with a bare `nvidia-smi` and counts as a host driver.
+// Without that variable the mirror does what the reference would do there -- and fails the same way.
+static std::string runDriverValidation(const Runtime &rt, bool silent, bool *isHostDriver) {
+    std::string driverRoot = "/run/nvidia/driver";
+    *isHostDriver = false;
+    struct stat st;
+    if (lstat("/host/usr/bin/nvidia-smi", &st) == 0 && st.st_size != 0) {
+        logInfo("Detected pre-installed driver on the host");
+        driverRoot = "/host";
+        *isHostDriver = true;
+    } else if (*envOr("GPUPROBE_HEADLESS", "") == '1' && !fileExists("/run/nvidia/driver/usr/bin/nvidia-smi")) {
+        *isHostDriver = true;
+        return runCommandMaybeWait(rt, {"nvidia-smi"}, silent);
+    }
+    if (!*isHostDriver) {
+        logInfo("Driver is not pre-installed on the host. Checking driver container status.");
+        std::string e = runCommandMaybeWait(rt, {"bash", "-c", std::string("stat ") + defaultStatusPath + "/.driver-ctr-ready"}, silent);
+        if (!e.empty()) return "error checking driver container status: " + e;
+    }
+    return runCommandMaybeWait(rt, {"chroot", driverRoot, "nvidia-smi"}, silent);
+}
+
 std::string validateDriver(Runtime &rt) {
     std::string e = deleteStatusFile(rt.flags.outputDir + "/" + driverStatusFile);
     if (!e.empty()) return e;
     e = deleteStatusFile(rt.flags.outputDir + "/" + hostDriverStatusFile);
     if (!e.empty()) return e;
-    // getDriverRoot (main.go:585-593): a pre-installed host driver is seen at /host; a driver container at
-    // /run/nvidia/driver. Headless boxes have neither mount, so fall back to the driver in this root.
     bool isHostDriver = false;
-    std::vector<std::string> cmd;
-    struct stat st;
-    if (lstat("/host/usr/bin/nvidia-smi", &st) == 0 && st.st_size != 0) {
-        logInfo("Detected pre-installed driver on the host");
-        isHostDriver = true;
-        cmd = {"chroot", "/host", "nvidia-smi"};
-    } else if (fileExists("/run/nvidia/driver/usr/bin/nvidia-smi")) {
-        cmd = {"chroot", "/run/nvidia/driver", "nvidia-smi"};
-    } else {
-        isHostDriver = true;
-        cmd = {"nvidia-smi"};
-    }
-    e = runCommandMaybeWait(rt, cmd, false);
+    e = runDriverValidation(rt, false, &isHostDriver);
     if (!e.empty()) {
         logError("driver is not ready");
         return e;
@@ -798,74 +811,165 @@ static void gauge(std::ostringstream &o, const char *name, const char *help, con
       << name << "{node=\"" << node << "\"} " << sprintfStr("%.10g", v) << "\n";
 }
 
+// NodeMetrics (metrics.go:52-70): the gauge values. Watcher threads write them on the reference's cadence; a scrape
+// only formats them, so nothing slow (nvidia-smi, lspci, a file read) ever sits on the scrape path.
+namespace {
+struct NodeMetricsState {
+    std::mutex mu;
+    double metricsReady = 0;
+    double driverReady = 0, toolkitReady = 0, pluginReady = 0, cudaReady = 0;
+    double driverValidation = 0, driverValidationLastSuccess = 0;
+    double deviceCount = 0, pluginValidationLastSuccess = 0;
+    double nvidiaPciDevices = 0;
+    std::string probeProm;  // gpuprobe-results.prom with @NODE@ filled in
+};
+NodeMetricsState g_nm;
+
+// statusFileCheckDelaySeconds = 30, driverValidationCheckDelaySeconds = 60, pluginValidationCheckDelaySeconds = 30
+// (metrics.go:40-47). GPUPROBE_WATCH_MS_PER_SECOND (tests) scales a "second" of those delays, default 1000 ms.
+void watchSleep(int seconds) {
+    const int msPerSecond = std::max(1, atoi(envOr("GPUPROBE_WATCH_MS_PER_SECOND", "1000")));
+    std::this_thread::sleep_for(std::chrono::milliseconds(static_cast<long long>(seconds) * msPerSecond));
+}
+
+// watchStatusFile (metrics.go:159-190): stat every 30 s, flip the gauge and log on a transition.
+void watchStatusFile(const Flags f, double NodeMetricsState::*gaugeField, const char *statusFile) {
+    logInfo("metrics: StatusFile: watching %s", statusFile);
+    bool prevReady = false;
+    for (;;) {
+        bool ready = fileExists(f.outputDir + "/" + statusFile);
+        if (!ready && !strcmp(statusFile, driverStatusFile)) ready = fileExists(f.outputDir + "/" + hostDriverStatusFile);  // :169-173
+        if (ready != prevReady) {
+            prevReady = ready;
+            logInfo("metrics: StatusFile: '%s' is %s", statusFile, ready ? "ready" : "not ready");
+            std::lock_guard<std::mutex> lock(g_nm.mu);
+            g_nm.*gaugeField = ready ? 1.0 : 0.0;
+        }
+        watchSleep(30);
+    }
+}
+
+// watchDriverValidation (metrics.go:237-250): Driver.runValidation(silent) every 60 s.
+void watchDriverValidation(const Runtime *rt) {
+    for (;;) {
+        bool isHostDriver = false;
+        Runtime once;  // no wait loop inside the watcher: one attempt per period
+        once.flags = rt->flags;
+        once.flags.withWait = false;
+        const bool ok = runDriverValidation(once, true, &isHostDriver).empty();
+        {
+            std::lock_guard<std::mutex> lock(g_nm.mu);
+            g_nm.driverValidation = ok ? 1.0 : 0.0;
+            if (ok) g_nm.driverValidationLastSuccess = static_cast<double>(time(nullptr));
+        }
+        watchSleep(60);
+    }
+}
+
+// watchDevicePluginValidation (metrics.go:192-235): countGPUResources every 30 s, log when the count changes.
+void watchDevicePluginValidation(const Flags f) {
+    logInfo("metrics: DevicePlugin validation: node name is %s", f.nodeName.c_str());
+    auto node = makeLocalNodeResources();
+    long long prevCount = -2;
+    for (;;) {
+        ResourceList cap, alloc;
+        const std::string e = node->get(&cap, &alloc);
+        long long count = -1;
+        {
+            std::lock_guard<std::mutex> lock(g_nm.mu);
+            if (!e.empty()) {
+                g_nm.deviceCount = -1;
+            } else {
+                count = countGPUResources(cap);
+                g_nm.deviceCount = static_cast<double>(count);
+                if (count != 0) g_nm.pluginValidationLastSuccess = static_cast<double>(time(nullptr));
+            }
+        }
+        if (prevCount != count) {
+            if (!e.empty()) logError("metrics: DevicePlugin validation: could not list the DevicePlugin devices: %s", e.c_str());
+            else logInfo("metrics: DevicePlugin validation: found %lld GPUs exposed by the DevicePlugin", count);
+        }
+        prevCount = count;
+        watchSleep(30);
+    }
+}
+
+// watchNVIDIAPCI (metrics.go:252-301): `lspci`, count the lines that mention nvidia, every 60 s.
+void watchNVIDIAPCI() {
+    int prev = -2;
+    for (;;) {
+        int devCount = -1;
+        if (FILE *p = popen("lspci 2>/dev/null", "r")) {
+            char line[1024];
+            int n = 0;
+            while (fgets(line, sizeof(line), p)) {
+                for (char *c = line; *c; ++c) *c = static_cast<char>(tolower(static_cast<unsigned char>(*c)));
+                if (strstr(line, "nvidia")) ++n;
+            }
+            if (pclose(p) == 0) devCount = n;
+        }
+        if (prev != devCount) {
+            if (devCount < 0) logError("metrics: PCI devices: Error running 'lspci'");
+            else logInfo("metrics: PCI devices: found %d NVIDIA device%s", devCount, devCount > 1 ? "s" : "");
+        }
+        prev = devCount;
+        {
+            std::lock_guard<std::mutex> lock(g_nm.mu);
+            g_nm.nvidiaPciDevices = devCount;
+        }
+        watchSleep(60);
+    }
+}
+
+// New (integration/validator/gpuprobe_metrics.go watchProbeResults): the probe's figures, re-read every 30 s.
+void watchProbeResults(const Flags f) {
+    const std::string path = f.outputDir + "/" + probeResultsProm;
+    logInfo("metrics: gpuprobe: watching %s", path.c_str());
+    for (;;) {
+        std::ifstream prom(path);
+        std::string text, line;
+        while (prom && std::getline(prom, line)) {
+            size_t at;
+            while ((at = line.find("@NODE@")) != std::string::npos) line.replace(at, 6, f.nodeName);
+            text += line + "\n";
+        }
+        {
+            std::lock_guard<std::mutex> lock(g_nm.mu);
+            g_nm.probeProm = text;
+        }
+        watchSleep(30);
+    }
+}
+}  // namespace
+
 std::string renderMetrics(const Flags &f, double metricsReadyTs) {
     std::ostringstream o;
     const std::string &node = f.nodeName;
-    auto ready = [&](const char *file) { return fileExists(f.outputDir + "/" + file) ? 1.0 : 0.0; };
+    std::lock_guard<std::mutex> lock(g_nm.mu);
     // names and help strings: validator/metrics.go:77-155
     gauge(o, "gpu_operator_node_metrics_ready_ts_seconds",
           "timestamp (in seconds) of the launch time of the GPU Operator node metrics Pod", node, metricsReadyTs);
     gauge(o, "gpu_operator_node_driver_ready",
-          "1 if the driver synchronization barrier of the the local node is open, 0 otherwise", node,
-          (ready(driverStatusFile) > 0 || ready(hostDriverStatusFile) > 0) ? 1.0 : 0.0);  // metrics.go:169-173
+          "1 if the driver synchronization barrier of the the local node is open, 0 otherwise", node, g_nm.driverReady);
     gauge(o, "gpu_operator_node_toolkit_ready",
-          "1 if the container-toolkit synchronization barrier on the local node is open, 0 otherwise", node, ready(toolkitStatusFile));
+          "1 if the container-toolkit synchronization barrier on the local node is open, 0 otherwise", node, g_nm.toolkitReady);
     gauge(o, "gpu_operator_node_plugin_ready",
-          "1 if the device plugin synchronization barrier on the local is open, 0 otherwise", node, ready(pluginStatusFile));
+          "1 if the device plugin synchronization barrier on the local is open, 0 otherwise", node, g_nm.pluginReady);
     gauge(o, "gpu_operator_node_cuda_ready", "1 if cuda synchronization barrier on the local node is open, 0 otherwise", node,
-          ready(cudaStatusFile));
-    // The reference samples these with watcher goroutines every 30-60 s (metrics.go:192-301); here they are
-    // evaluated per scrape and cached for the same periods.
-    struct Slow {
-        time_t driverAt = 0, pluginAt = 0, pciAt = 0;
-        double driverOk = 0, driverLastSuccess = 0, devices = -1, pluginLastSuccess = 0, pci = -1;
-    };
-    static Slow slow;
-    const time_t now = time(nullptr);
-    if (now - slow.driverAt >= 60) {  // watchDriverValidation: `nvidia-smi` (chroot'ed in-cluster), metrics.go:237-250
-        slow.driverAt = now;
-        const bool ok = system("nvidia-smi > /dev/null 2>&1") == 0;
-        slow.driverOk = ok ? 1 : 0;
-        if (ok) slow.driverLastSuccess = static_cast<double>(now);
-    }
-    if (now - slow.pluginAt >= 30) {  // watchDevicePluginValidation: countGPUResources, metrics.go:192-235
-        slow.pluginAt = now;
-        ResourceList cap, alloc;
-        if (makeLocalNodeResources()->get(&cap, &alloc).empty()) {
-            slow.devices = static_cast<double>(countGPUResources(cap));
-            if (slow.devices > 0) slow.pluginLastSuccess = static_cast<double>(now);
-        } else {
-            slow.devices = -1;
-        }
-    }
-    if (now - slow.pciAt >= 60) {  // watchNVIDIAPCI: `lspci | grep -i nvidia`, metrics.go:252-301
-        slow.pciAt = now;
-        slow.pci = -1;
-        if (FILE *p = popen("lspci 2>/dev/null | grep -ci nvidia", "r")) {
-            int n = -1;
-            if (fscanf(p, "%d", &n) == 1) slow.pci = n;
-            if (pclose(p) != 0 && slow.pci <= 0) slow.pci = -1;
-        }
-    }
+          g_nm.cudaReady);
     gauge(o, "gpu_operator_node_driver_validation", "1 if the driver validation test passed on the local node, 0 otherwise", node,
-          slow.driverOk);
+          g_nm.driverValidation);
     gauge(o, "gpu_operator_node_driver_validation_last_success_ts_seconds",
-          "timestamp (in seconds) of the last successful driver test validation", node, slow.driverLastSuccess);
+          "timestamp (in seconds) of the last successful driver test validation", node, g_nm.driverValidationLastSuccess);
     gauge(o, "gpu_operator_node_device_plugin_devices_total",
-          "number of GPU devices exposed by the DevicePlugin on the local node. -1 if failing to inspect the node spec.", node, slow.devices);
+          "number of GPU devices exposed by the DevicePlugin on the local node. -1 if failing to inspect the node spec.", node,
+          g_nm.deviceCount);
     gauge(o, "gpu_operator_node_device_plugin_validation_last_success_ts_seconds",
-          "timestamp (in seconds) of the last time GPU devices were found on the local node spec", node, slow.pluginLastSuccess);
-    gauge(o, "gpu_operator_nvidia_pci_devices_total", "number of NVIDIA devices found in the node. -1 if failing to count", node, slow.pci);
+          "timestamp (in seconds) of the last time GPU devices were found on the local node spec", node, g_nm.pluginValidationLastSuccess);
+    gauge(o, "gpu_operator_nvidia_pci_devices_total", "number of NVIDIA devices found in the node. -1 if failing to count", node,
+          g_nm.nvidiaPciDevices);
     // new gauges: the probe's achieved bandwidth, written by the workload next to the ready files
-    std::ifstream prom(f.outputDir + "/" + probeResultsProm);
-    if (prom) {
-        std::string line;
-        while (std::getline(prom, line)) {
-            size_t at;
-            while ((at = line.find("@NODE@")) != std::string::npos) line.replace(at, 6, node);
-            o << line << "\n";
-        }
-    }
+    o << g_nm.probeProm;
     return o.str();
 }
 
@@ -884,7 +988,16 @@ std::string runMetrics(Runtime &rt) {
         close(srv);
         return e;
     }
-    logInfo("metrics: serving /metrics on :%d", rt.flags.metricsPort);
+    // NodeMetrics.Run (metrics.go:304-320): stamp the start time, start the watchers, serve.
+    std::thread(watchStatusFile, rt.flags, &NodeMetricsState::driverReady, driverStatusFile).detach();
+    std::thread(watchStatusFile, rt.flags, &NodeMetricsState::toolkitReady, toolkitStatusFile).detach();
+    std::thread(watchStatusFile, rt.flags, &NodeMetricsState::pluginReady, pluginStatusFile).detach();
+    std::thread(watchStatusFile, rt.flags, &NodeMetricsState::cudaReady, cudaStatusFile).detach();
+    std::thread(watchDriverValidation, &rt).detach();
+    std::thread(watchDevicePluginValidation, rt.flags).detach();
+    std::thread(watchNVIDIAPCI).detach();
+    std::thread(watchProbeResults, rt.flags).detach();
+    logInfo("Running the metrics server, listening on :%d/metrics", rt.flags.metricsPort);
     for (;;) {
         int c = accept(srv, nullptr, nullptr);
         if (c < 0) {

@@ -370,9 +370,12 @@ def test_metrics_component_serves_reference_gauges_plus_probe_gauges(tmp_path):
     out = tmp_path / "v"
     out.mkdir()
     port = _free_port()
-    e = {"PATH": os.environ["PATH"]}
+    # the watchers run on the reference's cadence (status files and probe results every 30 s, driver and PCI every 60 s,
+    # metrics.go:40-47); the test shrinks a "second" of those delays to 1 ms
+    e = {"PATH": os.environ["PATH"], "GPUPROBE_WATCH_MS_PER_SECOND": "1"}
+    errlog = open(tmp_path / "metrics.stderr", "w")
     p = subprocess.Popen([VALIDATOR, "-c", "metrics", "-n", "node-a", "-p", str(port), "-o", str(out)], env=e,
-                         stderr=subprocess.PIPE, text=True)
+                         stderr=errlog, text=True)
     try:
         def scrape():
             for _ in range(100):
@@ -397,12 +400,61 @@ def test_metrics_component_serves_reference_gauges_plus_probe_gauges(tmp_path):
         (out / "host-driver-ready").write_text("")  # metrics.go:169-173: either driver file opens the barrier
         (out / "gpuprobe-results.prom").write_text(
             '# TYPE gpu_operator_node_cuda_hbm_gbps gauge\ngpu_operator_node_cuda_hbm_gbps{node="@NODE@",gpu="0"} 7126.5\n')
-        m = scrape()
+        for _ in range(200):  # the gauges follow at the watchers' next pass, not at the scrape
+            m = scrape()
+            if 'gpu_operator_node_cuda_hbm_gbps{node="node-a",gpu="0"} 7126.5' in m and 'cuda_ready{node="node-a"} 1' in m \
+                    and 'driver_ready{node="node-a"} 1' in m:
+                break
+            time.sleep(0.02)
         assert 'gpu_operator_node_cuda_ready{node="node-a"} 1' in m
         assert 'gpu_operator_node_driver_ready{node="node-a"} 1' in m
         assert 'gpu_operator_node_cuda_hbm_gbps{node="node-a",gpu="0"} 7126.5' in m
+        (out / "cuda-ready").unlink()
+        for _ in range(200):
+            m = scrape()
+            if 'cuda_ready{node="node-a"} 0' in m:
+                break
+            time.sleep(0.02)
+        assert 'gpu_operator_node_cuda_ready{node="node-a"} 0' in m
         with pytest.raises(urllib.error.HTTPError):
             urllib.request.urlopen(f"http://127.0.0.1:{port}/nope", timeout=2)
     finally:
         p.terminate()
         p.wait(timeout=5)
+        errlog.close()
+    log = (tmp_path / "metrics.stderr").read_text()
+    # transitions are logged the way watchStatusFile logs them (metrics.go:176-186)
+    assert "metrics: StatusFile: watching cuda-ready" in log
+    assert "metrics: StatusFile: 'cuda-ready' is ready" in log and "metrics: StatusFile: 'cuda-ready' is not ready" in log
+    assert "Running the metrics server, listening on :%d/metrics" % port in log
+
+
+def test_driver_component_follows_the_reference_outside_a_driver_container(tmp_path):
+    """Driver.runValidation (main.go:609-628) on a box with neither /host nor /run/nvidia/driver: the reference asks
+    for /run/nvidia/validations/.driver-ctr-ready first and fails there; so does the mirror."""
+    if os.path.exists("/host/usr/bin/nvidia-smi") or os.path.exists("/run/nvidia/validations/.driver-ctr-ready"):
+        pytest.skip("this box looks like a driver container")
+    out = tmp_path / "v"
+    r = run(["-c", "driver", "-o", str(out)])
+    assert r.returncode == 1
+    assert r.stderr.strip().splitlines()[-1].startswith(
+        "Error: error validating driver installation: error checking driver container status: exit status")
+    assert not (out / "driver-ready").exists() and not (out / "host-driver-ready").exists()
+
+
+def test_driver_component_headless_switch_checks_the_local_driver(tmp_path):
+    """GPUPROBE_HEADLESS=1 (tools/full_pass.py): a bare `nvidia-smi` stands in and the result counts as a host driver."""
+    if os.path.exists("/host/usr/bin/nvidia-smi") or os.path.exists("/run/nvidia/driver/usr/bin/nvidia-smi"):
+        pytest.skip("this box looks like a driver container")
+    fake = tmp_path / "bin"
+    fake.mkdir()
+    (fake / "nvidia-smi").write_text("#!/bin/sh\necho fake driver ok\n")
+    (fake / "nvidia-smi").chmod(0o755)
+    out = tmp_path / "v"
+    r = run(["-c", "driver", "-o", str(out)], {"GPUPROBE_HEADLESS": "1", "PATH": f"{fake}:{os.environ['PATH']}"})
+    assert r.returncode == 0, r.stderr
+    assert (out / "host-driver-ready").exists() and not (out / "driver-ready").exists()
+    (fake / "nvidia-smi").write_text("#!/bin/sh\nexit 9\n")
+    r = run(["-c", "driver", "-o", str(out)], {"GPUPROBE_HEADLESS": "1", "PATH": f"{fake}:{os.environ['PATH']}"})
+    assert r.returncode == 1 and "error validating driver installation: exit status 9" in r.stderr
+    assert not (out / "host-driver-ready").exists()  # deleted at the start of the run (main.go:639-649)

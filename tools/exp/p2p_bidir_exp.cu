@@ -190,6 +190,7 @@ int main(int argc, char **argv) {
         k_bulk<CH, SG, T, SUM><<<r.sms * CT, T, sm, st>>>(s, d, b, r.sum); CK(cudaGetLastError()); }
 
     for (int dirs : {1, 2}) {
+        if (getenv("P2P_EXP_CE_ONLY")) break;
         for (int mode : {0, 1}) {
             run("ldst_v16_u8_t512_x4", LDST(16, 8, 512, 4), mode, dirs);   // the product kernel's shape
             run("ldst_v32_u4_t512_x4", LDST(32, 4, 512, 4), mode, dirs);
@@ -207,6 +208,12 @@ int main(int argc, char **argv) {
             run("bulk_1k_s16_x8", BULK(1024, 16, 128, 8, true), mode, dirs);
         }
     }
+    // the copy engines, for reference: what the hardware moves without any SM in the path (no checksum possible)
+    for (int dirs : {1, 2}) {
+        run("copy_engine_memcpy", [&](Side &, const char *s, char *d, size_t b, cudaStream_t st) { CK(cudaMemcpyAsync(d, s, b, cudaMemcpyDeviceToDevice, st)); }, 0, dirs);
+        run("copy_engine_memcpy", [&](Side &, const char *s, char *d, size_t b, cudaStream_t st) { CK(cudaMemcpyAsync(d, s, b, cudaMemcpyDeviceToDevice, st)); }, 1, dirs);
+    }
+    if (getenv("P2P_EXP_CE_ONLY")) return 0;
     run("split_ldst_v16_u8_t512_x2", LDST(16, 8, 512, 2), 2, 2);
     run("split_bulk_16k_s6_x1", BULK(16384, 6, 128, 1, true), 2, 2);
     return 0;

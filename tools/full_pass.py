@@ -20,7 +20,7 @@ def full_pass(vadd_elems=0, p2p_bytes=0, ar_count=0, poll_ms=50, out_dir=None):
     out = out_dir or tempfile.mkdtemp(prefix="validations-")
     base = {"PATH": os.environ["PATH"], "OUTPUT_DIR": out, "NODE_NAME": os.uname().nodename, "OPERATOR_NAMESPACE": "gpu-operator",
             "GPUPROBE_MANIFEST_DIR": os.path.join(VDIR, "manifests"), "GPUPROBE_BIN_DIR": os.path.join(VDIR, "bin"),
-            "GPUPROBE_POLL_MS": str(poll_ms), "VALIDATOR_IMAGE": "headless", "LD_LIBRARY_PATH": os.environ.get("LD_LIBRARY_PATH", "")}
+            "GPUPROBE_POLL_MS": str(poll_ms), "VALIDATOR_IMAGE": "headless", "GPUPROBE_HEADLESS": "1", "LD_LIBRARY_PATH": os.environ.get("LD_LIBRARY_PATH", "")}
     base.update({k: v for k, v in os.environ.items() if k.startswith("GPUPROBE_") and k not in base})
     if vadd_elems:
         base["GPUPROBE_VADD_ELEMS"] = str(vadd_elems)
