@@ -45,7 +45,7 @@ UNIT = "GB/s"
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the default kernel at n = 2^30: not measurable inside a
 # timed run (a number taken under a profiler is never a bench value), so the line carries the figure of the committed
 # ncu --set full capture and says where it came from.
-NCU_TRAFFIC = {"bytes": 12_850_400_000, "source": "profiles/r01_vadd_ncu_full.md (ncu --set full, vadd_tile_kernel<4,1>, n=2^30)"}
+NCU_TRAFFIC = {"bytes": 12_848_950_000, "source": "profiles/r02_vadd_ncu_full.md (ncu --set full on the final tree, vadd_tile_kernel<4,1,0>, n=2^30, 3 launches)"}
 CPU_SAMPLE_LOG2 = 28
 SUSTAINED_SECONDS = 5.0
 FABRIC_BYTES = 1 << 30      # per directed pair (BASELINE.json configs[2])
