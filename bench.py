@@ -240,7 +240,8 @@ def fabric_block(gp, world: int) -> tuple[dict, bool]:
     nwords = FABRIC_BYTES // 4
     want = [oc.p2p_checksum(nwords, 0, s) for s in range(world)]
     pairs = [(s, t) for s in range(world) for t in range(world) if s != t]
-    for key, mode in (("p2p_serial", gp.P2P_SERIAL), ("p2p_rounds", gp.P2P_ROUNDS), ("p2p_rounds_push", gp.P2P_ROUNDS_PUSH)):
+    for key, mode in (("p2p_serial", gp.P2P_SERIAL), ("p2p_rounds", gp.P2P_ROUNDS), ("p2p_rounds_push", gp.P2P_ROUNDS_PUSH),
+                      ("p2p_rounds_copy_engine", gp.P2P_ROUNDS_CE)):
         try:
             rc, cells = gp.p2p_matrix(world, FABRIC_BYTES, iters=5, warmup=2, mode=mode, raise_on_fail=False)
             g = [cells[s][t].gbps for s, t in pairs]
@@ -254,7 +255,7 @@ def fabric_block(gp, world: int) -> tuple[dict, bool]:
             fabric[key] = {"error": str(e)}
             ok = False
     digests: dict = {}
-    for impl in ("nccl", "auto", "nvls", "two_shot", "hybrid", "push"):
+    for impl in ("nccl", "auto", "nvls", "two_shot", "hybrid", "push", "copy_engine"):
         try:
             r = gp.ALLREDUCE_IMPLS[impl](world, FABRIC_AR_COUNT, iters=10, warmup=3)
             if r.rounds not in digests:

@@ -292,7 +292,7 @@ extern "C" int gpuprobe_p2p_matrix(const gpuprobe_p2p_cfg *cfg, gpuprobe_p2p_cel
     }
     const int nd = cfg->ndev;
     if (nd < 2 || nd > MAX_DEVICES || cfg->iters < 1 || cfg->warmup < 0 || cfg->bytes_per_pair == 0 ||
-        (cfg->bytes_per_pair & 15u) || cfg->mode < GPUPROBE_P2P_SERIAL || cfg->mode > GPUPROBE_P2P_SERIAL_PUSH) {
+        (cfg->bytes_per_pair & 15u) || cfg->mode < GPUPROBE_P2P_SERIAL || cfg->mode > GPUPROBE_P2P_ROUNDS_CE) {
         set_err(err, errlen, "bad p2p cfg: ndev=%d bytes=%llu iters=%d warmup=%d mode=%d", nd,
                 (unsigned long long)cfg->bytes_per_pair, cfg->iters, cfg->warmup, cfg->mode);
         return GPUPROBE_EINVAL;
@@ -406,7 +406,9 @@ extern "C" int gpuprobe_p2p_matrix(const gpuprobe_p2p_cfg *cfg, gpuprobe_p2p_cel
                                         static_cast<int>(P2PB_SMEM)));
         }
     const bool push = cfg->mode == GPUPROBE_P2P_ROUNDS_PUSH || cfg->mode == GPUPROBE_P2P_SERIAL_PUSH;
-    const bool serial = cfg->mode == GPUPROBE_P2P_SERIAL || cfg->mode == GPUPROBE_P2P_SERIAL_PUSH;
+    const bool serial = cfg->mode == GPUPROBE_P2P_SERIAL || cfg->mode == GPUPROBE_P2P_SERIAL_PUSH || cfg->mode == GPUPROBE_P2P_SERIAL_CE;
+    // CE modes: the destination's copy engine moves the bytes; no kernel of ours is in the timed region
+    const bool ce = cfg->mode == GPUPROBE_P2P_SERIAL_CE || cfg->mode == GPUPROBE_P2P_ROUNDS_CE;
     auto runner = [&](int s, int t) { return push ? s : t; };
     // One timed launch of src -> dst on the running device's stream (events recorded around it).
     auto launch_pair = [&](int s, int t, bool timed) -> cudaError_t {
@@ -414,7 +416,9 @@ extern "C" int gpuprobe_p2p_matrix(const gpuprobe_p2p_cfg *cfg, gpuprobe_p2p_cel
         cudaError_t e = cudaSetDevice(dd.ord);
         if (e != cudaSuccess) return e;
         if (timed && (e = cudaEventRecord(dd.ev0, dd.st->stream)) != cudaSuccess) return e;
-        if (bulk)
+        if (ce) {
+            if ((e = cudaMemcpyPeerAsync(D[t].dst, D[t].ord, D[s].src, D[s].ord, bytes, dd.st->stream)) != cudaSuccess) return e;
+        } else if (bulk)
             p2p_bulk_copy_checksum_kernel<<<p2p_bulk_grid(*dd.st, bytes), P2PB_THREADS, P2PB_SMEM, dd.st->stream>>>(
                 reinterpret_cast<const unsigned char *>(D[s].src), reinterpret_cast<unsigned char *>(D[t].dst), bytes, dd.scr);
         else
@@ -441,6 +445,10 @@ extern "C" int gpuprobe_p2p_matrix(const gpuprobe_p2p_cfg *cfg, gpuprobe_p2p_cel
         expect[s].wait();
         c.checksum_expected = D[s].exp_sum;
         c.xor_expected = D[s].exp_xor;
+        if (ce) {  // no kernel saw the words in flight: the landed copy's digest is the checksum
+            head.out_sum = land_sum;
+            head.out_xor = land_xor;
+        }
         c.checksum_got = head.out_sum;
         c.xor_got = head.out_xor;
         c.verified = (head.out_sum == D[s].exp_sum && head.out_xor == D[s].exp_xor && land_sum == D[s].exp_sum &&

@@ -39,7 +39,7 @@ VARIANT_NAMES = {
     6: "tma_16k", 7: "persist128", 8: "scalar", 9: "tma_8k", 10: "ldg256_u2_ef", 11: "ldg128_u1", 12: "ldg256_u1", 13: "small",
 }
 
-P2P_SERIAL, P2P_ROUNDS, P2P_ROUNDS_PUSH, P2P_SERIAL_PUSH = 0, 1, 2, 3
+P2P_SERIAL, P2P_ROUNDS, P2P_ROUNDS_PUSH, P2P_SERIAL_PUSH, P2P_SERIAL_CE, P2P_ROUNDS_CE = 0, 1, 2, 3, 4, 5
 
 
 class DevInfo(C.Structure):
@@ -90,8 +90,8 @@ class ArResult(C.Structure):
                 ("impl", C.c_int)]
 
 
-AR_IMPL_NCCL, AR_IMPL_NVLS, AR_IMPL_P2P, AR_IMPL_HYBRID, AR_IMPL_PUSH = 0, 1, 2, 3, 4
-AR_IMPL_NAMES = {0: "nccl", 1: "nvls", 2: "two_shot", 3: "hybrid", 4: "push"}
+AR_IMPL_NCCL, AR_IMPL_NVLS, AR_IMPL_P2P, AR_IMPL_HYBRID, AR_IMPL_PUSH, AR_IMPL_CE = 0, 1, 2, 3, 4, 5
+AR_IMPL_NAMES = {0: "nccl", 1: "nvls", 2: "two_shot", 3: "hybrid", 4: "push", 5: "copy_engine"}
 
 
 class GpuProbeError(RuntimeError):
@@ -132,6 +132,7 @@ SIGNATURES = {
     "gpuprobe_allreduce_i32_hybrid": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
     "gpuprobe_allreduce_i32_push": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
     "gpuprobe_allreduce_i32_auto": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
+    "gpuprobe_allreduce_i32_ce": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
     "gpuprobe_shutdown": (None, []),
 }
 
@@ -341,6 +342,12 @@ def allreduce_i32_push(ndev: int, count: int, iters: int = 20, warmup: int = 5, 
     return _allreduce("gpuprobe_allreduce_i32_push", ndev, count, iters, warmup, seed, devs, peak_gbps)
 
 
+def allreduce_i32_ce(ndev: int, count: int, iters: int = 20, warmup: int = 5, seed: int = 0, devs=None,
+                     peak_gbps: float = 0.0) -> ArResult:
+    """gpuprobe_allreduce_i32_ce: two-shot with the copy engines moving the data and a kernel adding."""
+    return _allreduce("gpuprobe_allreduce_i32_ce", ndev, count, iters, warmup, seed, devs, peak_gbps)
+
+
 def allreduce_i32_auto(ndev: int, count: int, iters: int = 20, warmup: int = 5, seed: int = 0, devs=None,
                        peak_gbps: float = 0.0) -> ArResult:
     """gpuprobe_allreduce_i32_auto: the library's own choice of hand-written kernel for this rank count."""
@@ -348,7 +355,8 @@ def allreduce_i32_auto(ndev: int, count: int, iters: int = 20, warmup: int = 5, 
 
 
 ALLREDUCE_IMPLS = {"nccl": allreduce_i32, "nvls": allreduce_i32_nvls, "two_shot": allreduce_i32_p2p,
-                   "hybrid": allreduce_i32_hybrid, "push": allreduce_i32_push, "auto": allreduce_i32_auto}
+                   "hybrid": allreduce_i32_hybrid, "push": allreduce_i32_push, "copy_engine": allreduce_i32_ce,
+                   "auto": allreduce_i32_auto}
 
 
 def shutdown() -> None:

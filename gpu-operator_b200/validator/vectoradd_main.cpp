@@ -11,10 +11,10 @@
 //            GPUPROBE_VADD_ELEMS   HBM bandwidth run on every visible GPU
 //            GPUPROBE_P2P_BYTES    all-pairs NVLink copy+checksum (>= 2 GPUs)
 //            GPUPROBE_AR_COUNT     int32 allreduce over all visible GPUs; GPUPROBE_AR_IMPL = nccl (default) | auto |
-//                                  nvls | p2p | hybrid | push | both.  If NCCL cannot be loaded (the validator image
+//                                  nvls | p2p | hybrid | push | ce | both.  If NCCL cannot be loaded (the validator image
 //                                  strips the CUDA user libraries) the library's own kernel runs instead and the
 //                                  result says so, unless GPUPROBE_AR_REQUIRE_NCCL=1 makes that a failure.
-//            GPUPROBE_P2P_MODE     serial (default) | serial_push | rounds | rounds_push
+//            GPUPROBE_P2P_MODE     serial (default) | serial_push | rounds | rounds_push | serial_ce | rounds_ce
 //            GPUPROBE_MIN_HBM_FRAC / GPUPROBE_MIN_LINK_FRAC  fail below this fraction of 8000 / 900 GB/s
 //   Results go to $OUTPUT_DIR/gpuprobe-results.json and .prom when that directory exists.
 #include <sys/stat.h>
@@ -165,6 +165,8 @@ int main(void) {
             if (!strcmp(m, "serial_push")) cfg.mode = GPUPROBE_P2P_SERIAL_PUSH;
             else if (!strcmp(m, "rounds")) cfg.mode = GPUPROBE_P2P_ROUNDS;
             else if (!strcmp(m, "rounds_push")) cfg.mode = GPUPROBE_P2P_ROUNDS_PUSH;
+            else if (!strcmp(m, "serial_ce")) cfg.mode = GPUPROBE_P2P_SERIAL_CE;
+            else if (!strcmp(m, "rounds_ce")) cfg.mode = GPUPROBE_P2P_ROUNDS_CE;
         }
         std::vector<gpuprobe_p2p_cell> cells(static_cast<size_t>(ndev) * ndev);
         rc = gpuprobe_p2p_matrix(&cfg, cells.data(), err, sizeof(err));
@@ -199,7 +201,7 @@ int main(void) {
         cfg.warmup = 5;
         gpuprobe_ar_result r{};
         // GPUPROBE_AR_IMPL: "nccl" (default; validates the library path), "auto" (the library's choice of hand-written
-        // kernel for this rank count; "kernel" is the round-1 spelling), "nvls" / "p2p" / "hybrid" / "push" (one kernel),
+        // kernel for this rank count; "kernel" is the round-1 spelling), "nvls" / "p2p" / "hybrid" / "push" / "ce" (one of them),
         // "both" (NCCL result reported, NCCL and the auto kernel must both verify)
         const char *impl = getenv("GPUPROBE_AR_IMPL") ? getenv("GPUPROBE_AR_IMPL") : "nccl";
         const char *implRan = impl;
@@ -211,6 +213,8 @@ int main(void) {
             rc = gpuprobe_allreduce_i32_hybrid(&cfg, &r, err, sizeof(err));
         } else if (!strcmp(impl, "push")) {
             rc = gpuprobe_allreduce_i32_push(&cfg, &r, err, sizeof(err));
+        } else if (!strcmp(impl, "ce") || !strcmp(impl, "copy_engine")) {
+            rc = gpuprobe_allreduce_i32_ce(&cfg, &r, err, sizeof(err));
         } else if (!strcmp(impl, "auto") || !strcmp(impl, "kernel")) {
             rc = gpuprobe_allreduce_i32_auto(&cfg, &r, err, sizeof(err));
         } else {

@@ -124,6 +124,12 @@ typedef struct gpuprobe_vadd_result {
 #define GPUPROBE_P2P_ROUNDS 1 /* ndev-1 rounds, dst = (src + r) mod ndev, all pairs of a round concurrently */
 #define GPUPROBE_P2P_ROUNDS_PUSH 2 /* same schedule, but the kernel runs on src and STORES into dst over NVLink */
 #define GPUPROBE_P2P_SERIAL_PUSH 3 /* one directed pair at a time, kernel on src storing into dst               */
+/* The same schedules with the destination's COPY ENGINE moving the bytes (cudaMemcpyPeerAsync) and the checksum taken
+ * from the landed copy by the digest kernel afterwards.  Not the probe north_star describes (no SM touches the link), but
+ * the reference point a validator needs beside it: DMA transfers use larger link packets than SM loads/stores can, so
+ * they show what the links themselves carry (about 770 GB/s per direction even with every GPU sending and receiving). */
+#define GPUPROBE_P2P_SERIAL_CE 4
+#define GPUPROBE_P2P_ROUNDS_CE 5
 
 typedef struct gpuprobe_p2p_cfg {
     int ndev;
@@ -179,6 +185,7 @@ typedef struct gpuprobe_ar_result {
 #define GPUPROBE_AR_IMPL_P2P 2    /* two-shot: pull-reduce the slice, push the sum            */
 #define GPUPROBE_AR_IMPL_HYBRID 3
 #define GPUPROBE_AR_IMPL_PUSH 4   /* two-shot with posted writes only (scatter, add, broadcast) */
+#define GPUPROBE_AR_IMPL_CE 5     /* two-shot with the copy engines moving the data, a kernel adding */
 
 /* ---- library / device queries --------------------------------------------------- */
 
@@ -308,6 +315,13 @@ GPUPROBE_API int gpuprobe_allreduce_i32_hybrid(const gpuprobe_ar_cfg *cfg, gpupr
  * the opposite direction of the links; costs (nd-1)/nd of the payload in extra device memory per rank and a
  * third in-kernel synchronisation.  ndev must be 2, 4 or 8; works with or without multicast.  No reference counterpart. */
 GPUPROBE_API int gpuprobe_allreduce_i32_push(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
+
+/* (c-ce) Two-shot with every transfer done by the GPUs' copy engines (cudaMemcpyPeerAsync, ordered by events across
+ * the devices' streams) and only the addition in a kernel, chunked so that the add overlaps the transfers.  Exists because
+ * of a measurement (profiles/r02_fabric.md): SM-issued loads and stores cross NVLink in 128-byte packets and top out at
+ * 667-700 GB/s of payload per direction when both directions are busy, DMA transfers reach 770.  Any ndev >= 2; needs
+ * peer access, not multicast; uses (ndev-1)/ndev of the payload in staging memory per rank.  No reference counterpart. */
+GPUPROBE_API int gpuprobe_allreduce_i32_ce(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
 
 /* The hand-written kernel the validator uses when GPUPROBE_AR_IMPL does not name one: the measured best for the
  * rank count (all-push two-shot at 2 ranks, hybrid at 4 and 8; profiles/r02_fabric.md), falling back to the

@@ -160,7 +160,7 @@ def test_bad_arguments_are_rejected_before_touching_a_device(gp):
     assert rc == gp.EINVAL
     rc, _ = gp.p2p_matrix(2, 1000, raise_on_fail=False)  # not a multiple of 16
     assert rc == gp.EINVAL
-    rc, _ = gp.p2p_matrix(2, 1 << 20, mode=5, raise_on_fail=False)  # modes are 0..2
+    rc, _ = gp.p2p_matrix(2, 1 << 20, mode=6, raise_on_fail=False)  # modes are 0..5
     assert rc == gp.EINVAL
     with pytest.raises(gp.GpuProbeError) as e:
         gp.allreduce_i32(1, 1024)

@@ -135,6 +135,33 @@ def test_push_two_shot_allreduce_kernel_bit_exact(gp, ndev, count):
         assert res.impl == gp.AR_IMPL_PUSH
 
 
+@pytest.mark.parametrize("count", AR_COUNTS + [31, 33, (1 << 21) + 1, (3 << 20) + 64])
+def test_copy_engine_two_shot_allreduce_bit_exact(gp, ndev, count, monkeypatch):
+    """Copy engines move every byte (cudaMemcpyPeerAsync ordered by events across the GPUs' streams), a kernel adds;
+    chunk counts from one to more than the default, sizes that leave empty slices and ragged last chunks."""
+    for chunks in ("1", "4", "16"):
+        monkeypatch.setenv("GPUPROBE_CE_CHUNKS", chunks)
+        for nd in [n for n in (2, 3, 4, 8) if n <= ndev]:
+            res = gp.allreduce_i32_ce(nd, count, iters=3, warmup=2, seed=12)
+            assert_reduced_buffer_matches_oracle(res, nd, count, 12, 2, 3)
+            assert res.impl == gp.AR_IMPL_CE
+
+
+@pytest.mark.parametrize("mode", [4, 5])
+def test_p2p_copy_engine_modes_land_the_oracles_words(gp, ndev, mode):
+    """SERIAL_CE / ROUNDS_CE: the destination's copy engine moves the bytes; the checksum is the digest of the landed copy."""
+    nd = min(ndev, 8)
+    nbytes = (32 << 20) + 16 * 3
+    rc, cells = gp.p2p_matrix(nd, nbytes, iters=2, warmup=1, mode=mode, seed=5)
+    assert rc == gp.OK
+    for s in range(nd):
+        want = oc.p2p_checksum(nbytes // 4, 5, s)
+        for t in range(nd):
+            if s != t:
+                c = cells[s][t]
+                assert c.verified == 1 and (c.checksum_got, c.xor_got) == want and c.gbps > 50
+
+
 def test_auto_allreduce_picks_a_kernel_and_matches_oracle(gp, ndev):
     for nd in [n for n in (2, 4, 8) if n <= ndev]:
         res = gp.allreduce_i32_auto(nd, (8 << 20) + 9, iters=2, warmup=1, seed=11)

@@ -316,3 +316,69 @@ def test_concurrent_callers_on_one_device_are_serialised(gp):
     assert not errors, errors
     for n, seed, kind, s, x, bad in results.values():
         assert bad == 0 and (s, x) == oc.vectoradd_digest(n, seed, kind)
+
+
+def test_cached_staging_survives_growing_shrinking_and_shutdown(gp, torch_cuda, monkeypatch):
+    """The staging slots and pinned bounce buffers of gpuprobe_vectoradd_buffers are cached per device and only grow;
+    gpuprobe_shutdown frees them and the next call rebuilds them; GPUPROBE_BUF_CACHE=0 frees them after every call.
+    Every result is checked against the host loop, and the cache must not leak: device memory in use after the calls
+    is bounded by the largest staging set, and returns to the starting point after shutdown."""
+    torch = torch_cuda
+    torch.cuda.synchronize()
+    gp.shutdown()
+    free0, _ = torch.cuda.mem_get_info()
+    sizes = [50_000, 7, (9 << 20) + 5, 50_000, 1 << 20, (9 << 20) + 5, 3]
+    for rep, n in enumerate(sizes * 2):
+        a, b = oc.fill_inputs(n, seed=20 + rep, kind=rep % 3)
+        c = np.full(n, np.nan, dtype=np.float32)
+        gp.vectoradd_buffers(a, b, c, n)
+        assert oc.count_mismatch(c, oc.vectoradd(a, b)) == 0, (rep, n)
+        if rep == len(sizes) - 1:
+            gp.shutdown()  # mid-way: everything is rebuilt on demand
+    free1, _ = torch.cuda.mem_get_info()
+    assert free0 - free1 <= 3 * 3 * (8 << 20) * 4 + (64 << 20), "more device memory held than three slots of three 32 MiB chunks"
+    gp.shutdown()
+    free2, _ = torch.cuda.mem_get_info()
+    assert free2 >= free0 - (8 << 20)
+    monkeypatch.setenv("GPUPROBE_BUF_CACHE", "0")
+    for n in (50_000, (8 << 20) + 1):
+        a, b = oc.fill_inputs(n, seed=3, kind=0)
+        c = np.empty(n, dtype=np.float32)
+        gp.vectoradd_buffers(a, b, c, n)
+        assert oc.count_mismatch(c, oc.vectoradd(a, b)) == 0
+        free3, _ = torch.cuda.mem_get_info()
+        assert free3 >= free0 - (8 << 20), "GPUPROBE_BUF_CACHE=0 must give the staging back after the call"
+
+
+def test_digest_and_verify_share_cached_scratch_across_threads_and_streams(gp, torch_cuda):
+    """digest/verify use one cached scratch buffer per device; callers on different host threads and streams are
+    serialised on it inside the library and must all get the oracle's answer."""
+    import threading
+
+    torch = torch_cuda
+    n = (1 << 22) + 77
+    bufs, want = [], []
+    for i in range(4):
+        w = torch.empty(n, device="cuda", dtype=torch.float32)
+        gp.fill_inputs_device(w, None, n, seed=40 + i, gen_kind=gp.GEN_BITS)
+        bufs.append(w)
+        a, _ = oc.fill_inputs(n, seed=40 + i, kind=oc.GEN_BITS)
+        want.append(oc.digest(a))
+    torch.cuda.synchronize()
+    got, errors = {}, []
+
+    def work(i):
+        try:
+            s = torch.cuda.Stream()
+            for _ in range(20):
+                got[i] = gp.digest_device(bufs[i], n, stream=s.cuda_stream)
+                assert got[i] == want[i]
+        except Exception as e:  # noqa: BLE001
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(4)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors

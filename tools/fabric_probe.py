@@ -20,14 +20,14 @@ def main():
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--out", default="")
     ap.add_argument("--ar-sizes", default="", help="extra allreduce counts (log2 list) for a latency curve at max ndev")
-    ap.add_argument("--modes", default="serial,serial_push,rounds,rounds_push")
+    ap.add_argument("--modes", default="serial,serial_push,rounds,rounds_push,serial_ce,rounds_ce")
     ap.add_argument("--no-allreduce", action="store_true")
     args = ap.parse_args()
     gp = ge.load_package().gpuprobe
     nd = args.ndev or gp.device_count()
     res = {"ndev": nd, "bytes_per_pair": args.bytes}
     for name, mode in (("serial", gp.P2P_SERIAL), ("serial_push", gp.P2P_SERIAL_PUSH), ("rounds", gp.P2P_ROUNDS),
-                       ("rounds_push", gp.P2P_ROUNDS_PUSH)):
+                       ("rounds_push", gp.P2P_ROUNDS_PUSH), ("serial_ce", gp.P2P_SERIAL_CE), ("rounds_ce", gp.P2P_ROUNDS_CE)):
         if name not in args.modes.split(","):
             continue
         rc, cells = gp.p2p_matrix(nd, args.bytes, iters=args.iters, warmup=3, mode=mode, raise_on_fail=False)
