@@ -12,6 +12,7 @@
 #include <dlfcn.h>
 #include <nccl.h>
 
+#include "ce_twoshot.cuh"
 #include "common.cuh"
 #include "gen.cuh"
 
@@ -96,31 +97,6 @@ ar_verify_kernel(const uint32_t *__restrict__ x, uint64_t n, uint32_t seed, int 
     }
     bad = warp_sum_u64(bad);
     if ((threadIdx.x & 31) == 0 && bad) atomicAdd(mismatches, bad);
-}
-
-// Copy-engine two-shot, the arithmetic step: x[i] += sum over the staged copies of the same words. All operands are in
-// this GPU's HBM (the copy engines put them there); 128-bit accesses, grid-stride.
-__global__ void __launch_bounds__(256)
-ar_add_staged_kernel(uint32_t *__restrict__ x, const uint32_t *__restrict__ stage, uint64_t slot_stride, int nslots, uint64_t n) {
-    const uint64_t tid = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-    const uint64_t stride = static_cast<uint64_t>(gridDim.x) * blockDim.x;
-    const uint64_t n4 = n / 4;  // x, stage and slot_stride are 16-byte aligned (chunks start on 32-word boundaries)
-    for (uint64_t v = tid; v < n4; v += stride) {
-        uint4 acc = *reinterpret_cast<const uint4 *>(x + v * 4);
-        for (int s = 0; s < nslots; ++s) {
-            const uint4 t = ldg128_stream(stage + static_cast<uint64_t>(s) * slot_stride + v * 4);
-            acc.x += t.x;
-            acc.y += t.y;
-            acc.z += t.z;
-            acc.w += t.w;
-        }
-        *reinterpret_cast<uint4 *>(x + v * 4) = acc;
-    }
-    for (uint64_t i = n4 * 4 + tid; i < n; i += stride) {
-        uint32_t acc = x[i];
-        for (int s = 0; s < nslots; ++s) acc += stage[static_cast<uint64_t>(s) * slot_stride + i];
-        x[i] = acc;
-    }
 }
 
 struct ArDev {
@@ -310,25 +286,14 @@ extern "C" int gpuprobe_allreduce_i32(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_re
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// Copy-engine two-shot (gpuprobe_allreduce_i32_ce). Measured on this fabric (profiles/r02_fabric.md): loads and stores
-// issued by SMs cross NVLink as 128-byte packets (1.125 / 1.1875 link bytes per payload byte, 667-700 GB/s per direction
-// with both directions busy), while the DMA engines move 770 GB/s per direction in the same situation. So this variant
-// lets the copy engines do every transfer and keeps only the arithmetic in a kernel:
-//   scatter  rank r copies its words of slice q into a staging slot in q's memory      (n-1 peer copies per chunk)
-//   add      rank q adds the n-1 staged copies to its own words of slice q             (ar_add_staged_kernel, local HBM)
-//   gather   rank q copies the reduced slice q into every rank's buffer                (n-1 peer copies per chunk)
-// Slices are cut into chunks so that the add of chunk k runs while the engines move chunks k+1 (scatter) and k-1
-// (gather); ordering is by CUDA events across the GPUs' streams (one process drives all GPUs), no kernel ever waits on
-// another GPU. Peers are visited in rotated order so that every GPU receives from one sender at a time.
+// gpuprobe_allreduce_i32_ce: the copy-engine two-shot (ce_twoshot.cuh) over the whole buffer.
 namespace gp {
 struct CeDev {
     int ord = -1;
     DeviceState *st = nullptr;
     uint32_t *buf = nullptr, *stage = nullptr;
     unsigned long long *bad = nullptr;
-    cudaStream_t s_scatter = nullptr, s_gather = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_go = nullptr, ev_gathered = nullptr;
-    std::vector<cudaEvent_t> ev_scattered, ev_added;  // per chunk
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 };
 }  // namespace gp
 
@@ -363,31 +328,20 @@ extern "C" int gpuprobe_allreduce_i32_ce(const gpuprobe_ar_cfg *cfg, gpuprobe_ar
     for (int i : order) locks.emplace_back(D[i].st->mu);
 
     const uint64_t count = cfg->count;
-    uint64_t per = (count + nd - 1) / nd;
-    per = (per + 31) & ~31ull;  // slice q = [q*per, min((q+1)*per, count))
-    auto slice_lo = [&](int q) { return std::min<uint64_t>(per * static_cast<uint64_t>(q), count); };
-    auto slice_len = [&](int q) { return std::min<uint64_t>(slice_lo(q) + per, count) - slice_lo(q); };
-    // chunks: enough of them that the add overlaps the transfers, few enough that a copy stays large
-    int chunks = 2;  // measured at 2 ranks, 1 GiB: 1 chunk 635, 2 chunks 748, 4 731, 8 699, 16 647 GB/s (profiles/r02_fabric.md)
-    if (const char *e = getenv("GPUPROBE_CE_CHUNKS")) chunks = std::max(1, std::min(64, atoi(e)));
-    while (chunks > 1 && per / chunks < (1u << 18)) chunks /= 2;
-    const uint64_t chunk_words = ((per + chunks - 1) / chunks + 31) & ~31ull;
-
+    CeTwoShot engine;
     auto cleanup = [&]() {
         for (auto &d : D) {
             if (cudaSetDevice(d.ord) != cudaSuccess) continue;
             cudaDeviceSynchronize();
+        }
+        engine.destroy();
+        for (auto &d : D) {
+            if (cudaSetDevice(d.ord) != cudaSuccess) continue;
             cudaFree(d.buf);
             cudaFree(d.stage);
             cudaFree(d.bad);
-            if (d.s_scatter) cudaStreamDestroy(d.s_scatter);
-            if (d.s_gather) cudaStreamDestroy(d.s_gather);
-            for (cudaEvent_t e : {d.ev0, d.ev1, d.ev_go, d.ev_gathered})
-                if (e) cudaEventDestroy(e);
-            for (cudaEvent_t e : d.ev_scattered)
-                if (e) cudaEventDestroy(e);
-            for (cudaEvent_t e : d.ev_added)
-                if (e) cudaEventDestroy(e);
+            if (d.ev0) cudaEventDestroy(d.ev0);
+            if (d.ev1) cudaEventDestroy(d.ev1);
         }
         (void)cudaGetLastError();
     };
@@ -423,125 +377,58 @@ extern "C" int gpuprobe_allreduce_i32_ce(const gpuprobe_ar_cfg *cfg, gpuprobe_ar
     const uint64_t bytes = count * sizeof(uint32_t);
     out->ndev = nd;
     out->bytes = bytes;
+    std::vector<CeRank> ranks(nd);
     for (int r = 0; r < nd; ++r) {
         CeDev &d = D[r];
         GP_TRY(cudaSetDevice(d.ord));
         GP_TRY(cudaMalloc(&d.buf, bytes));
-        GP_TRY(cudaMalloc(&d.stage, static_cast<size_t>(nd - 1) * per * sizeof(uint32_t)));
+        GP_TRY(cudaMalloc(&d.stage, CeTwoShot::stage_words(count, nd) * sizeof(uint32_t)));
         GP_TRY(cudaMalloc(&d.bad, sizeof(unsigned long long)));
         GP_TRY(cudaMemsetAsync(d.bad, 0, sizeof(unsigned long long), d.st->stream));
-        GP_TRY(cudaStreamCreateWithFlags(&d.s_scatter, cudaStreamNonBlocking));
-        GP_TRY(cudaStreamCreateWithFlags(&d.s_gather, cudaStreamNonBlocking));
         GP_TRY(cudaEventCreate(&d.ev0));
         GP_TRY(cudaEventCreate(&d.ev1));
-        GP_TRY(cudaEventCreateWithFlags(&d.ev_go, cudaEventDisableTiming));
-        GP_TRY(cudaEventCreateWithFlags(&d.ev_gathered, cudaEventDisableTiming));
-        d.ev_scattered.assign(chunks, nullptr);
-        d.ev_added.assign(chunks, nullptr);
-        for (auto &e : d.ev_scattered) GP_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-        for (auto &e : d.ev_added) GP_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         rc = launch_fill_words(*d.st, d.buf, count, hash_base(cfg->seed, stream_ar(r)), d.st->stream, err, errlen);
         if (rc) {
             cleanup();
             return rc;
         }
+        ranks[r].ord = d.ord;
+        ranks[r].sm_count = d.st->sm_count;
+        ranks[r].buf = d.buf;
+        ranks[r].stage = d.stage;
+        ranks[r].main = d.st->stream;
     }
+    GP_TRY(engine.init(ranks, count, 0));
     for (auto &d : D) {
         GP_TRY(cudaSetDevice(d.ord));
         GP_TRY(cudaStreamSynchronize(d.st->stream));
     }
 
-    // words [off, off+len) of chunk k inside a slice of `len_slice` words
-    auto chunk_range = [&](uint64_t len_slice, int k, uint64_t *off, uint64_t *len) {
-        *off = std::min<uint64_t>(chunk_words * static_cast<uint64_t>(k), len_slice);
-        *len = std::min<uint64_t>(*off + chunk_words, len_slice) - *off;
-    };
-    // One in-place round, issued asynchronously on every GPU's streams.
-    auto issue_round = [&](bool timed) -> cudaError_t {
-        cudaError_t e;
-        for (int r = 0; r < nd; ++r) {  // start: the main stream has waited for the whole previous round (see the end)
-            CeDev &d = D[r];
-            if ((e = cudaSetDevice(d.ord)) != cudaSuccess) return e;
-            if (timed && (e = cudaEventRecord(d.ev0, d.st->stream)) != cudaSuccess) return e;
-            if ((e = cudaEventRecord(d.ev_go, d.st->stream)) != cudaSuccess) return e;
-            if ((e = cudaStreamWaitEvent(d.s_scatter, d.ev_go, 0)) != cudaSuccess) return e;
-            if ((e = cudaStreamWaitEvent(d.s_gather, d.ev_go, 0)) != cudaSuccess) return e;
-        }
-        for (int k = 0; k < chunks; ++k)  // scatter: chunk by chunk, every rank, peers in rotated order
-            for (int r = 0; r < nd; ++r) {
-                CeDev &d = D[r];
-                if ((e = cudaSetDevice(d.ord)) != cudaSuccess) return e;
-                for (int j = 1; j < nd; ++j) {
-                    const int q = (r + j) % nd;
-                    uint64_t off, len;
-                    chunk_range(slice_len(q), k, &off, &len);
-                    if (!len) continue;
-                    const int slot = r < q ? r : r - 1;
-                    e = cudaMemcpyPeerAsync(D[q].stage + static_cast<uint64_t>(slot) * per + off, D[q].ord, d.buf + slice_lo(q) + off, d.ord,
-                                            len * sizeof(uint32_t), d.s_scatter);
-                    if (e != cudaSuccess) return e;
-                }
-                if ((e = cudaEventRecord(d.ev_scattered[k], d.s_scatter)) != cudaSuccess) return e;
-            }
-        for (int k = 0; k < chunks; ++k)  // add, then gather the reduced chunk to everyone
-            for (int q = 0; q < nd; ++q) {
-                CeDev &d = D[q];
-                if ((e = cudaSetDevice(d.ord)) != cudaSuccess) return e;
-                for (int r = 0; r < nd; ++r)
-                    if (r != q && (e = cudaStreamWaitEvent(d.st->stream, D[r].ev_scattered[k], 0)) != cudaSuccess) return e;
-                uint64_t off, len;
-                chunk_range(slice_len(q), k, &off, &len);
-                if (len) {
-                    const uint64_t want = (len / 4 + 255) / 256;
-                    const int grid = static_cast<int>(std::max<uint64_t>(1, std::min<uint64_t>(want, static_cast<uint64_t>(d.st->sm_count) * 8)));
-                    ar_add_staged_kernel<<<grid, 256, 0, d.st->stream>>>(d.buf + slice_lo(q) + off, d.stage + off, per, nd - 1, len);
-                    if ((e = cudaGetLastError()) != cudaSuccess) return e;
-                }
-                if ((e = cudaEventRecord(d.ev_added[k], d.st->stream)) != cudaSuccess) return e;
-                if ((e = cudaStreamWaitEvent(d.s_gather, d.ev_added[k], 0)) != cudaSuccess) return e;
-                for (int j = 1; j < nd && len; ++j) {
-                    const int p = (q + j) % nd;
-                    e = cudaMemcpyPeerAsync(D[p].buf + slice_lo(q) + off, D[p].ord, d.buf + slice_lo(q) + off, d.ord, len * sizeof(uint32_t),
-                                            d.s_gather);
-                    if (e != cudaSuccess) return e;
-                }
-            }
-        for (auto &d : D) {
-            if ((e = cudaSetDevice(d.ord)) != cudaSuccess) return e;
-            if ((e = cudaEventRecord(d.ev_gathered, d.s_gather)) != cudaSuccess) return e;
-        }
-        for (auto &d : D) {  // end of the round on every main stream: every gather, incoming and outgoing, has landed
-            if ((e = cudaSetDevice(d.ord)) != cudaSuccess) return e;
-            for (auto &x : D)
-                if ((e = cudaStreamWaitEvent(d.st->stream, x.ev_gathered, 0)) != cudaSuccess) return e;
-            if (timed && (e = cudaEventRecord(d.ev1, d.st->stream)) != cudaSuccess) return e;
-        }
-        return cudaSuccess;
-    };
-    auto sync_all = [&]() -> cudaError_t {
-        for (auto &d : D) {
-            cudaError_t e = cudaSetDevice(d.ord);
-            if (e == cudaSuccess) e = cudaStreamSynchronize(d.st->stream);
-            if (e != cudaSuccess) return e;
-        }
-        return cudaSuccess;
-    };
-
     std::vector<float> ms;
     const int total = std::max(1, cfg->warmup) + cfg->iters;
     for (int it = 0; it < total; ++it) {
         const bool timed = it >= total - cfg->iters;
-        GP_TRY(issue_round(timed));
-        GP_TRY(sync_all());
-        if (timed) {
-            float worst = 0;
+        if (timed)
             for (auto &d : D) {
+                GP_TRY(cudaSetDevice(d.ord));
+                GP_TRY(cudaEventRecord(d.ev0, d.st->stream));
+            }
+        GP_TRY(engine.issue_round());
+        float worst = 0;
+        for (auto &d : D) {
+            GP_TRY(cudaSetDevice(d.ord));
+            if (timed) GP_TRY(cudaEventRecord(d.ev1, d.st->stream));
+        }
+        for (auto &d : D) {
+            GP_TRY(cudaSetDevice(d.ord));
+            GP_TRY(cudaStreamSynchronize(d.st->stream));
+            if (timed) {
                 float m = 0;
                 GP_TRY(cudaEventElapsedTime(&m, d.ev0, d.ev1));
                 worst = std::max(worst, m);
             }
-            ms.push_back(worst);
         }
+        if (timed) ms.push_back(worst);
     }
 
     uint32_t mult = 1;

@@ -22,6 +22,7 @@
 #include <cooperative_groups.h>
 #include <cuda.h>
 
+#include "ce_twoshot.cuh"
 #include "common.cuh"
 #include "gen.cuh"
 
@@ -58,6 +59,7 @@ struct NvlsArgs {
     int barrier_peer;       // 1: no multicast on this box -- barrier through per-rank flag slots written with peer stores
     int st_v4;              // NVLS part: broadcast with 16-byte multimem.st (four sums per store) instead of 4-byte ones
     uint64_t stage_off;     // algo 3: word offset of the staging area (nranks-1 slices) behind the payload of every rank
+    uint64_t reduce_count;  // words [0, reduce_count) are reduced by this kernel (= count, except in the NVLS + copy-engine hybrid)
     uint32_t *peer[NVLS_MAX_PEERS];  // algo 1: unicast mapping of every rank's buffer (peer[rank] == local)
 };
 
@@ -275,9 +277,9 @@ __global__ void __launch_bounds__(NVLS_THREADS) nvls_allreduce_kernel(NvlsArgs a
     } else if (a.phases & NVLS_REDUCE) {
         cross_gpu_barrier(grid, a, bar++);  // every rank's inputs are in place (and last round's stores have landed)
         // my slice, rounded so that warps stay on 128-byte lines
-        uint64_t per = (a.count + a.nranks - 1) / a.nranks;
+        uint64_t per = (a.reduce_count + a.nranks - 1) / a.nranks;
         per = (per + 31) & ~31ull;
-        const uint64_t lo = min(per * a.rank, a.count), hi = min(lo + per, a.count);
+        const uint64_t lo = min(per * a.rank, a.reduce_count), hi = min(lo + per, a.reduce_count);
         auto p2p_part = [&](uint64_t from, uint64_t to, uint64_t tid0, uint64_t stride0) {
             switch (a.nranks) {
             case 2: p2p_reduce_broadcast<2>(a, from, to, tid0, stride0); break;
@@ -434,6 +436,9 @@ struct NvlsDev {
     int *error = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int grid = 0;
+    // NVLS + copy engines: the stream the engine's round is ordered on, and the two events that tie it to the main stream
+    cudaStream_t ce_main = nullptr;
+    cudaEvent_t ev_round = nullptr, ev_ce_done = nullptr;
 };
 
 }  // namespace gp
@@ -452,11 +457,11 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
                 (unsigned long long)cfg->count, cfg->iters, cfg->warmup);
         return GPUPROBE_EINVAL;
     }
-    if (algo >= 1 && nd != 2 && nd != 4 && nd != 8) {
+    if (algo >= 1 && algo <= 3 && nd != 2 && nd != 4 && nd != 8) {
         set_err(err, errlen, "the peer two-shot allreduce is built for 2, 4 or 8 ranks (got %d)", nd);
         return GPUPROBE_EINVAL;
     }
-    const char *algo_name = algo == 0 ? "nvls" : algo == 1 ? "two-shot" : algo == 2 ? "hybrid" : "push two-shot";
+    const char *algo_name = algo == 0 ? "nvls" : algo == 1 ? "two-shot" : algo == 2 ? "hybrid" : algo == 3 ? "push two-shot" : "nvls + copy engines";
     std::vector<NvlsDev> D(nd);
     int rc;
     for (int i = 0; i < nd; ++i) {
@@ -499,7 +504,8 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
     for (int i : order) locks.emplace_back(D[i].st->mu);
 
     // tuning knobs (defaults are the measured best; see profiles/)
-    int unroll = 8, ctas_per_sm = 2;
+    // algo 4 keeps half of every SM free: the copy-engine side's add kernel has to run beside the resident multimem kernel
+    int unroll = 8, ctas_per_sm = algo == 4 ? 1 : 2;
     if (const char *u = getenv("GPUPROBE_NVLS_UNROLL")) unroll = atoi(u);
     if (const char *c = getenv("GPUPROBE_NVLS_CTAS")) ctas_per_sm = std::max(1, atoi(c));
     int st_v4 = 0;  // 16-byte multimem.st: measured in profiles/r02_fabric.md
@@ -517,7 +523,17 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
     uint64_t per_words = (cfg->count + nd - 1) / nd;
     per_words = (per_words + 31) & ~31ull;  // as in the kernel
     const uint64_t stage_off_words = (cfg->count + 31) & ~31ull;
-    const uint64_t data_bytes = algo == 3 ? (stage_off_words + static_cast<uint64_t>(nd - 1) * per_words) * sizeof(uint32_t) : payload;
+    // NVLS + copy engines (algo 4): the multimem kernel reduces words [0, head), the copy-engine two-shot words [head, count)
+    // at the same time; the engine's staging slices sit behind the payload like the push kernel's
+    int nvlsce_permille = 800;
+    if (const char *h = getenv("GPUPROBE_NVLSCE_PERMILLE")) nvlsce_permille = std::max(1, std::min(999, atoi(h)));
+    uint64_t head_words = cfg->count;
+    if (algo == 4) head_words = std::min<uint64_t>(cfg->count, (cfg->count / 1000u * static_cast<uint64_t>(nvlsce_permille) + 31) & ~31ull);
+    const uint64_t tail_words = cfg->count - head_words;
+    const uint64_t data_bytes = algo == 3   ? (stage_off_words + static_cast<uint64_t>(nd - 1) * per_words) * sizeof(uint32_t)
+                                : algo == 4 ? (stage_off_words + CeTwoShot::stage_words(tail_words, nd)) * sizeof(uint32_t)
+                                            : payload;
+    CeTwoShot engine;
     CUmemGenericAllocationHandle mc_handle = 0;
     CUdeviceptr mc_va = 0;
     bool mc_created = false, mc_mapped = false;
@@ -527,10 +543,17 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
         for (auto &d : D) {
             if (cudaSetDevice(d.ord) != cudaSuccess) continue;
             cudaDeviceSynchronize();
+        }
+        engine.destroy();
+        for (auto &d : D) {
+            if (cudaSetDevice(d.ord) != cudaSuccess) continue;
             cudaFree(d.bad);
             cudaFree(d.error);
             if (d.ev0) cudaEventDestroy(d.ev0);
             if (d.ev1) cudaEventDestroy(d.ev1);
+            if (d.ev_round) cudaEventDestroy(d.ev_round);
+            if (d.ev_ce_done) cudaEventDestroy(d.ev_ce_done);
+            if (d.ce_main) cudaStreamDestroy(d.ce_main);
         }
         if (mc_mapped) g_drv.MemUnmap(mc_va, size);
         if (mc_va) g_drv.MemAddressFree(mc_va, size);
@@ -637,6 +660,24 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
         GP_TRY(cudaStreamSynchronize(d.st->stream));
     }
 
+    const bool ce_tail = algo == 4 && tail_words > 0;
+    if (ce_tail) {
+        std::vector<CeRank> ranks(nd);
+        for (int r = 0; r < nd; ++r) {
+            NvlsDev &d = D[r];
+            GP_TRY(cudaSetDevice(d.ord));
+            GP_TRY(cudaStreamCreateWithFlags(&d.ce_main, cudaStreamNonBlocking));
+            GP_TRY(cudaEventCreateWithFlags(&d.ev_round, cudaEventDisableTiming));
+            GP_TRY(cudaEventCreateWithFlags(&d.ev_ce_done, cudaEventDisableTiming));
+            ranks[r].ord = d.ord;
+            ranks[r].sm_count = d.st->sm_count;
+            ranks[r].buf = reinterpret_cast<uint32_t *>(d.uc) + head_words;
+            ranks[r].stage = reinterpret_cast<uint32_t *>(d.uc) + stage_off_words;
+            ranks[r].main = d.ce_main;
+        }
+        GP_TRY(engine.init(ranks, tail_words, 0));
+    }
+
     uint32_t barriers_done = 0;
     auto launch_all = [&](int phases, uint32_t mult, bool timed) -> cudaError_t {
         for (int r = 0; r < nd; ++r) {
@@ -651,13 +692,14 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
             a.mismatches = d.bad;
             a.error = d.error;
             a.count = cfg->count;
+            a.reduce_count = head_words;
             a.seed = cfg->seed;
             a.mult = mult;
             a.barrier_base = barriers_done;
             a.rank = r;
             a.nranks = nd;
             a.phases = phases;
-            a.algo = algo;
+            a.algo = algo == 4 ? 0 : algo;
             a.barrier_peer = use_mc ? 0 : 1;
             a.st_v4 = st_v4;
             a.stage_off = stage_off_words;
@@ -666,11 +708,29 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
             for (int q = 0; q < NVLS_MAX_PEERS; ++q) a.peer[q] = q < nd ? reinterpret_cast<uint32_t *>(D[q].uc) : nullptr;
             void *args[] = {&a};
             if (timed && (e = cudaEventRecord(d.ev0, d.st->stream)) != cudaSuccess) return e;
+            if (ce_tail && (phases & NVLS_REDUCE)) {  // the engine's round starts with the kernel, not after it
+                if ((e = cudaEventRecord(d.ev_round, d.st->stream)) != cudaSuccess) return e;
+                if ((e = cudaStreamWaitEvent(d.ce_main, d.ev_round, 0)) != cudaSuccess) return e;
+            }
             e = cudaLaunchCooperativeKernel(kernel_fn, dim3(d.grid), dim3(NVLS_THREADS),
                                             args, 0, d.st->stream);
             if (e != cudaSuccess) return e;
-            if (timed && (e = cudaEventRecord(d.ev1, d.st->stream)) != cudaSuccess) return e;
         }
+        if (ce_tail && (phases & NVLS_REDUCE)) {
+            cudaError_t e = engine.issue_round();
+            if (e != cudaSuccess) return e;
+            for (auto &d : D) {  // the round is over on a rank when its kernel and the engine's round both are
+                if ((e = cudaSetDevice(d.ord)) != cudaSuccess) return e;
+                if ((e = cudaEventRecord(d.ev_ce_done, d.ce_main)) != cudaSuccess) return e;
+                if ((e = cudaStreamWaitEvent(d.st->stream, d.ev_ce_done, 0)) != cudaSuccess) return e;
+            }
+        }
+        if (timed)
+            for (auto &d : D) {
+                cudaError_t e = cudaSetDevice(d.ord);
+                if (e == cudaSuccess) e = cudaEventRecord(d.ev1, d.st->stream);
+                if (e != cudaSuccess) return e;
+            }
         if (phases & NVLS_REDUCE) barriers_done += 2;
         return cudaSuccess;
     };
@@ -683,8 +743,15 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
         return cudaSuccess;
     };
 
-    // round 1 is the fused launch: fill -> barrier -> reduce+broadcast -> barrier (no verify yet)
-    GP_TRY(launch_all(NVLS_FILL | NVLS_REDUCE, 1, false));
+    // round 1 is the fused launch: fill -> barrier -> reduce+broadcast -> barrier (no verify yet). With the copy engines
+    // in the round the fill is a launch of its own: the engines read the tail as soon as the round starts.
+    if (ce_tail) {
+        GP_TRY(launch_all(NVLS_FILL, 1, false));
+        GP_TRY(sync_all());
+        GP_TRY(launch_all(NVLS_REDUCE, 1, false));
+    } else {
+        GP_TRY(launch_all(NVLS_FILL | NVLS_REDUCE, 1, false));
+    }
     GP_TRY(sync_all());
     int rounds = 1;
     for (int i = 1; i < cfg->warmup; ++i, ++rounds) {
@@ -740,7 +807,8 @@ static int allreduce_symmetric(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *o
         }
     }
     out->rounds = static_cast<uint32_t>(rounds);
-    out->impl = algo == 0 ? GPUPROBE_AR_IMPL_NVLS : algo == 1 ? GPUPROBE_AR_IMPL_P2P : algo == 2 ? GPUPROBE_AR_IMPL_HYBRID : GPUPROBE_AR_IMPL_PUSH;
+    out->impl = algo == 0 ? GPUPROBE_AR_IMPL_NVLS : algo == 1 ? GPUPROBE_AR_IMPL_P2P : algo == 2 ? GPUPROBE_AR_IMPL_HYBRID
+                : algo == 3 ? GPUPROBE_AR_IMPL_PUSH : GPUPROBE_AR_IMPL_NVLS_CE;
     out->ndev = nd;
     out->nccl_version = 0;  // not NCCL
     out->bytes = payload;
@@ -779,6 +847,10 @@ extern "C" int gpuprobe_allreduce_i32_hybrid(const gpuprobe_ar_cfg *cfg, gpuprob
 
 extern "C" int gpuprobe_allreduce_i32_p2p(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen) {
     return allreduce_symmetric(cfg, out, 1, err, errlen);
+}
+
+extern "C" int gpuprobe_allreduce_i32_nvls_ce(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen) {
+    return allreduce_symmetric(cfg, out, 4, err, errlen);
 }
 
 extern "C" int gpuprobe_allreduce_i32_push(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen) {

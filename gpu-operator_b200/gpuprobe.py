@@ -90,8 +90,8 @@ class ArResult(C.Structure):
                 ("impl", C.c_int)]
 
 
-AR_IMPL_NCCL, AR_IMPL_NVLS, AR_IMPL_P2P, AR_IMPL_HYBRID, AR_IMPL_PUSH, AR_IMPL_CE = 0, 1, 2, 3, 4, 5
-AR_IMPL_NAMES = {0: "nccl", 1: "nvls", 2: "two_shot", 3: "hybrid", 4: "push", 5: "copy_engine"}
+AR_IMPL_NCCL, AR_IMPL_NVLS, AR_IMPL_P2P, AR_IMPL_HYBRID, AR_IMPL_PUSH, AR_IMPL_CE, AR_IMPL_NVLS_CE = 0, 1, 2, 3, 4, 5, 6
+AR_IMPL_NAMES = {0: "nccl", 1: "nvls", 2: "two_shot", 3: "hybrid", 4: "push", 5: "copy_engine", 6: "nvls_ce"}
 
 
 class GpuProbeError(RuntimeError):
@@ -133,6 +133,7 @@ SIGNATURES = {
     "gpuprobe_allreduce_i32_push": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
     "gpuprobe_allreduce_i32_auto": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
     "gpuprobe_allreduce_i32_ce": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
+    "gpuprobe_allreduce_i32_nvls_ce": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
     "gpuprobe_shutdown": (None, []),
 }
 
@@ -348,6 +349,12 @@ def allreduce_i32_ce(ndev: int, count: int, iters: int = 20, warmup: int = 5, se
     return _allreduce("gpuprobe_allreduce_i32_ce", ndev, count, iters, warmup, seed, devs, peak_gbps)
 
 
+def allreduce_i32_nvls_ce(ndev: int, count: int, iters: int = 20, warmup: int = 5, seed: int = 0, devs=None,
+                          peak_gbps: float = 0.0) -> ArResult:
+    """gpuprobe_allreduce_i32_nvls_ce: the multimem kernel on the head of the buffer, the copy-engine two-shot on the tail."""
+    return _allreduce("gpuprobe_allreduce_i32_nvls_ce", ndev, count, iters, warmup, seed, devs, peak_gbps)
+
+
 def allreduce_i32_auto(ndev: int, count: int, iters: int = 20, warmup: int = 5, seed: int = 0, devs=None,
                        peak_gbps: float = 0.0) -> ArResult:
     """gpuprobe_allreduce_i32_auto: the library's own choice of hand-written kernel for this rank count."""
@@ -356,7 +363,7 @@ def allreduce_i32_auto(ndev: int, count: int, iters: int = 20, warmup: int = 5, 
 
 ALLREDUCE_IMPLS = {"nccl": allreduce_i32, "nvls": allreduce_i32_nvls, "two_shot": allreduce_i32_p2p,
                    "hybrid": allreduce_i32_hybrid, "push": allreduce_i32_push, "copy_engine": allreduce_i32_ce,
-                   "auto": allreduce_i32_auto}
+                   "nvls_ce": allreduce_i32_nvls_ce, "auto": allreduce_i32_auto}
 
 
 def shutdown() -> None:

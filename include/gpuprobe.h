@@ -186,6 +186,7 @@ typedef struct gpuprobe_ar_result {
 #define GPUPROBE_AR_IMPL_HYBRID 3
 #define GPUPROBE_AR_IMPL_PUSH 4   /* two-shot with posted writes only (scatter, add, broadcast) */
 #define GPUPROBE_AR_IMPL_CE 5     /* two-shot with the copy engines moving the data, a kernel adding */
+#define GPUPROBE_AR_IMPL_NVLS_CE 6 /* the multimem kernel on the head of the buffer, the copy-engine two-shot on the tail */
 
 /* ---- library / device queries --------------------------------------------------- */
 
@@ -322,6 +323,13 @@ GPUPROBE_API int gpuprobe_allreduce_i32_push(const gpuprobe_ar_cfg *cfg, gpuprob
  * 667-700 GB/s of payload per direction when both directions are busy, DMA transfers reach 770.  Any ndev >= 2; needs
  * peer access, not multicast; uses (ndev-1)/ndev of the payload in staging memory per rank.  No reference counterpart. */
 GPUPROBE_API int gpuprobe_allreduce_i32_ce(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
+
+/* (c-nvls-ce) The switch and the copy engines at once: the multimem kernel (c') reduces the first
+ * GPUPROBE_NVLSCE_PERMILLE/1000 of the buffer (default 800) while the copy-engine two-shot (c-ce) reduces the rest, each
+ * on its own streams of every GPU.  The switch's reduction path sustains about 500 GB/s of link traffic per direction and
+ * leaves link time idle; DMA packets fill it better than SM-issued ones.  Needs multicast; any ndev >= 2.
+ * No reference counterpart. */
+GPUPROBE_API int gpuprobe_allreduce_i32_nvls_ce(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
 
 /* The hand-written kernel the validator uses when GPUPROBE_AR_IMPL does not name one: the measured best for the
  * rank count (all-push two-shot at 2 ranks, hybrid at 4 and 8; profiles/r02_fabric.md), falling back to the

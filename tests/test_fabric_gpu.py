@@ -147,6 +147,18 @@ def test_copy_engine_two_shot_allreduce_bit_exact(gp, ndev, count, monkeypatch):
             assert res.impl == gp.AR_IMPL_CE
 
 
+@pytest.mark.parametrize("count", [1, 1000, 4096 * 3 + 5, (4 << 20) + 7, (16 << 20) + 7])
+def test_nvls_plus_copy_engine_allreduce_bit_exact(gp, ndev, count, monkeypatch):
+    """The multimem kernel reduces the head of the buffer while the copy-engine two-shot reduces the tail; splits from
+    almost-all-switch to almost-all-engines, counts so small that the tail (or a slice of it) is empty."""
+    for permille in ("800", "100", "999"):
+        monkeypatch.setenv("GPUPROBE_NVLSCE_PERMILLE", permille)
+        for nd in [n for n in (2, 3, 4, 8) if n <= ndev]:
+            res = gp.allreduce_i32_nvls_ce(nd, count, iters=3, warmup=2, seed=13)
+            assert_reduced_buffer_matches_oracle(res, nd, count, 13, 2, 3)
+            assert res.impl == gp.AR_IMPL_NVLS_CE
+
+
 @pytest.mark.parametrize("mode", [4, 5])
 def test_p2p_copy_engine_modes_land_the_oracles_words(gp, ndev, mode):
     """SERIAL_CE / ROUNDS_CE: the destination's copy engine moves the bytes; the checksum is the digest of the landed copy."""

@@ -15,7 +15,7 @@ from oracle import oracle as oc  # noqa: E402  (a measurement tool, not the prod
 ap = argparse.ArgumentParser()
 ap.add_argument("--counts", default="10,20,24,28")
 ap.add_argument("--ndevs", default="")
-ap.add_argument("--impls", default="nvls,two_shot,hybrid,push,copy_engine,auto,nccl")
+ap.add_argument("--impls", default="nvls,two_shot,hybrid,push,copy_engine,nvls_ce,auto,nccl")
 ap.add_argument("--iters", type=int, default=20)
 ap.add_argument("--warmup", type=int, default=5)
 ap.add_argument("--tag", default="")
