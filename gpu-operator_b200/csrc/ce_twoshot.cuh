@@ -9,11 +9,14 @@
 //   gather   rank q copies the reduced slice q into every rank's buffer                (n-1 peer copies per chunk)
 // Slices are cut into chunks so that the add of chunk k runs while the engines move chunk k+1 (scatter) and k-1
 // (gather). Ordering is by CUDA events across the GPUs' streams (one process drives all GPUs); no kernel ever waits on
-// another GPU. Peers are visited in rotated order so that every GPU receives from one sender at a time.
+// another GPU. Every rank has one copy stream per peer and phase, so the n-1 transfers of a chunk run side by side, and
+// the whole round is replayed from one CUDA graph that spans all GPUs (one launch per round instead of hundreds of calls).
 //
 // Used by gpuprobe_allreduce_i32_ce (allreduce.cu, the whole buffer) and by the NVLS + copy-engine hybrid (nvls.cu, the
 // tail of the buffer while the multimem kernel reduces the head).
 #pragma once
+#include <string>
+
 #include "common.cuh"
 
 namespace gp {
@@ -76,13 +79,21 @@ public:
             Side &s = S_[r];
             int lo = 0, hi = 0;
             if ((e = cudaDeviceGetStreamPriorityRange(&lo, &hi)) != cudaSuccess) return e;
-            if ((e = cudaStreamCreateWithFlags(&s.scatter, cudaStreamNonBlocking)) != cudaSuccess) return e;
-            if ((e = cudaStreamCreateWithFlags(&s.gather, cudaStreamNonBlocking)) != cudaSuccess) return e;
+            // one copy stream per peer and phase: the n-1 transfers of a chunk run side by side, so the start-up gap
+            // of one copy is covered by the others (serial copies on one stream lose ~15 us per copy)
+            s.scatter.assign(nd_ - 1, nullptr);
+            s.gather.assign(nd_ - 1, nullptr);
+            for (auto &st : s.scatter)
+                if ((e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking)) != cudaSuccess) return e;
+            for (auto &st : s.gather)
+                if ((e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking)) != cudaSuccess) return e;
             // the add must not queue behind a long-running kernel of the caller on the same GPU
             if ((e = cudaStreamCreateWithPriority(&s.add, cudaStreamNonBlocking, hi)) != cudaSuccess) return e;
             if ((e = cudaEventCreateWithFlags(&s.go, cudaEventDisableTiming)) != cudaSuccess) return e;
-            if ((e = cudaEventCreateWithFlags(&s.gathered, cudaEventDisableTiming)) != cudaSuccess) return e;
-            s.scattered.assign(chunks_, nullptr);
+            s.gathered.assign(nd_ - 1, nullptr);
+            for (auto &ev : s.gathered)
+                if ((e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)) != cudaSuccess) return e;
+            s.scattered.assign(static_cast<size_t>(chunks_) * (nd_ - 1), nullptr);
             s.added.assign(chunks_, nullptr);
             for (auto &ev : s.scattered)
                 if ((e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)) != cudaSuccess) return e;
@@ -94,35 +105,145 @@ public:
 
     // One in-place round, issued asynchronously. Afterwards every rank's `main` stream waits for the whole round
     // (every gather, incoming and outgoing), so consecutive rounds and whatever the caller enqueues next are ordered.
+    //
+    // A round is some hundred stream operations (n(n-1) peer copies per chunk and phase, events between them), and a peer
+    // copy costs the host tens of microseconds to enqueue: issued call by call the host, not the links, bounds the round
+    // from 4 ranks up (measured: 4 chunks at 4 ranks 520 GB/s against 695 with 2). So the round is captured ONCE into a
+    // CUDA graph spanning all GPUs (stream capture forked from one origin stream through event waits) and replayed with
+    // one launch per round. If the capture is refused the round is issued directly, as before.
     cudaError_t issue_round() {
+        if (!graph_tried_) {
+            build_graph();
+            if (getenv("GPUPROBE_CE_DEBUG"))
+                fprintf(stderr, "gpuprobe: copy-engine two-shot, %d ranks, %d chunks: %s\n", nd_, chunks_,
+                        graph_exec_ ? "replaying a captured multi-GPU graph" : ("issuing call by call (" + graph_note_ + ")").c_str());
+        }
+        if (!graph_exec_) {
+            std::vector<cudaStream_t> mains(nd_);
+            for (int r = 0; r < nd_; ++r) mains[r] = R_[r].main;
+            return issue_direct(mains);
+        }
+        cudaError_t e;
+        if ((e = cudaSetDevice(R_[0].ord)) != cudaSuccess) return e;
+        for (int r = 0; r < nd_; ++r) {  // the replay starts after what every rank's main stream holds now ...
+            if ((e = cudaSetDevice(R_[r].ord)) != cudaSuccess) return e;
+            if ((e = cudaEventRecord(S_[r].ext_go, R_[r].main)) != cudaSuccess) return e;
+        }
+        if ((e = cudaSetDevice(R_[0].ord)) != cudaSuccess) return e;
+        for (int r = 0; r < nd_; ++r)
+            if ((e = cudaStreamWaitEvent(origin_, S_[r].ext_go, 0)) != cudaSuccess) return e;
+        if ((e = cudaGraphLaunch(graph_exec_, origin_)) != cudaSuccess) return e;
+        if ((e = cudaEventRecord(ext_done_, origin_)) != cudaSuccess) return e;
+        for (int r = 0; r < nd_; ++r) {  // ... and every main stream waits for the whole round
+            if ((e = cudaSetDevice(R_[r].ord)) != cudaSuccess) return e;
+            if ((e = cudaStreamWaitEvent(R_[r].main, ext_done_, 0)) != cudaSuccess) return e;
+        }
+        return cudaSuccess;
+    }
+
+    bool uses_graph() const { return graph_exec_ != nullptr; }
+
+private:
+    // Captures one round into a graph: origin_ forks every rank's internal main stream, issue_direct() does the rest.
+    void build_graph() {
+        graph_tried_ = true;
+        if (const char *g = getenv("GPUPROBE_CE_GRAPH"); g && *g == '0') return;
+        if (cudaSetDevice(R_[0].ord) != cudaSuccess) return;
+        bool ok = cudaStreamCreateWithFlags(&origin_, cudaStreamNonBlocking) == cudaSuccess &&
+                  cudaEventCreateWithFlags(&ext_done_, cudaEventDisableTiming) == cudaSuccess &&
+                  cudaEventCreateWithFlags(&fork_, cudaEventDisableTiming) == cudaSuccess;
+        std::vector<cudaStream_t> mains(nd_, nullptr);
+        for (int r = 0; r < nd_ && ok; ++r) {
+            ok = cudaSetDevice(R_[r].ord) == cudaSuccess && cudaStreamCreateWithFlags(&S_[r].gmain, cudaStreamNonBlocking) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&S_[r].ext_go, cudaEventDisableTiming) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&S_[r].join, cudaEventDisableTiming) == cudaSuccess;
+            mains[r] = S_[r].gmain;
+        }
+        if (!ok) {
+            (void)cudaGetLastError();
+            return;
+        }
+        cudaGraph_t graph = nullptr;
+        cudaSetDevice(R_[0].ord);
+        const char *step = "cudaStreamBeginCapture";
+        cudaError_t e = cudaStreamBeginCapture(origin_, cudaStreamCaptureModeRelaxed);
+        if (e != cudaSuccess) {
+            graph_note_ = std::string(step) + ": " + cudaGetErrorString(e);
+            (void)cudaGetLastError();
+            return;
+        }
+        step = "fork";
+        e = cudaEventRecord(fork_, origin_);
+        for (int r = 0; r < nd_ && e == cudaSuccess; ++r) {
+            if ((e = cudaSetDevice(R_[r].ord)) != cudaSuccess) break;
+            e = cudaStreamWaitEvent(mains[r], fork_, 0);
+        }
+        if (e == cudaSuccess) {
+            step = "capturing the round";
+            e = issue_direct(mains);
+        }
+        if (e == cudaSuccess) step = "join";
+        for (int r = 0; r < nd_ && e == cudaSuccess; ++r) {  // every forked stream joins the origin again
+            if ((e = cudaSetDevice(R_[r].ord)) != cudaSuccess) break;
+            if ((e = cudaEventRecord(S_[r].join, mains[r])) != cudaSuccess) break;
+        }
+        if (e == cudaSuccess) e = cudaSetDevice(R_[0].ord);
+        for (int r = 0; r < nd_ && e == cudaSuccess; ++r) e = cudaStreamWaitEvent(origin_, S_[r].join, 0);
+        cudaSetDevice(R_[0].ord);
+        const cudaError_t e_end = cudaStreamEndCapture(origin_, &graph);
+        if (e == cudaSuccess && e_end != cudaSuccess) {
+            step = "cudaStreamEndCapture";
+            e = e_end;
+        }
+        if (e == cudaSuccess && graph) {
+            step = "cudaGraphInstantiate";
+            e = cudaGraphInstantiate(&graph_exec_, graph, 0);
+        }
+        if (graph) cudaGraphDestroy(graph);
+        if (e != cudaSuccess) {
+            graph_exec_ = nullptr;
+            graph_note_ = std::string(step) + ": " + cudaGetErrorString(e);
+            (void)cudaGetLastError();
+        }
+    }
+
+    cudaError_t issue_direct(const std::vector<cudaStream_t> &mains) {
         cudaError_t e;
         for (int r = 0; r < nd_; ++r) {
             if ((e = cudaSetDevice(R_[r].ord)) != cudaSuccess) return e;
-            if ((e = cudaEventRecord(S_[r].go, R_[r].main)) != cudaSuccess) return e;
-            if ((e = cudaStreamWaitEvent(S_[r].scatter, S_[r].go, 0)) != cudaSuccess) return e;
-            if ((e = cudaStreamWaitEvent(S_[r].gather, S_[r].go, 0)) != cudaSuccess) return e;
+            if ((e = cudaEventRecord(S_[r].go, mains[r])) != cudaSuccess) return e;
+            for (auto &st : S_[r].scatter)
+                if ((e = cudaStreamWaitEvent(st, S_[r].go, 0)) != cudaSuccess) return e;
+            for (auto &st : S_[r].gather)
+                if ((e = cudaStreamWaitEvent(st, S_[r].go, 0)) != cudaSuccess) return e;
             if ((e = cudaStreamWaitEvent(S_[r].add, S_[r].go, 0)) != cudaSuccess) return e;
         }
-        for (int k = 0; k < chunks_; ++k)  // scatter: chunk by chunk, every rank, peers in rotated order
+        // stream j-1 of rank r serves peer (r + j) % n; event scattered[k*(n-1) + j-1] = "r's chunk k has reached that peer"
+        for (int k = 0; k < chunks_; ++k)
             for (int r = 0; r < nd_; ++r) {
                 if ((e = cudaSetDevice(R_[r].ord)) != cudaSuccess) return e;
                 for (int j = 1; j < nd_; ++j) {
                     const int q = (r + j) % nd_;
                     uint64_t off, len;
                     chunk_range(slice_len(q), k, &off, &len);
-                    if (!len) continue;
-                    const int slot = r < q ? r : r - 1;
-                    e = cudaMemcpyPeerAsync(R_[q].stage + static_cast<uint64_t>(slot) * per_ + off, R_[q].ord, R_[r].buf + slice_lo(q) + off,
-                                            R_[r].ord, len * sizeof(uint32_t), S_[r].scatter);
-                    if (e != cudaSuccess) return e;
+                    if (len) {
+                        const int slot = r < q ? r : r - 1;
+                        // unified addressing tells the driver which two devices these are; this form is also what stream capture takes
+                        e = cudaMemcpyAsync(R_[q].stage + static_cast<uint64_t>(slot) * per_ + off, R_[r].buf + slice_lo(q) + off,
+                                            len * sizeof(uint32_t), cudaMemcpyDeviceToDevice, S_[r].scatter[j - 1]);
+                        if (e != cudaSuccess) return e;
+                    }
+                    if ((e = cudaEventRecord(S_[r].scattered[static_cast<size_t>(k) * (nd_ - 1) + (j - 1)], S_[r].scatter[j - 1])) != cudaSuccess) return e;
                 }
-                if ((e = cudaEventRecord(S_[r].scattered[k], S_[r].scatter)) != cudaSuccess) return e;
             }
-        for (int k = 0; k < chunks_; ++k)  // add, then gather the reduced chunk to everyone
+        for (int k = 0; k < chunks_; ++k)  // add once every peer's copy of the chunk is here, then gather it to everyone
             for (int q = 0; q < nd_; ++q) {
                 if ((e = cudaSetDevice(R_[q].ord)) != cudaSuccess) return e;
-                for (int r = 0; r < nd_; ++r)
-                    if (r != q && (e = cudaStreamWaitEvent(S_[q].add, S_[r].scattered[k], 0)) != cudaSuccess) return e;
+                for (int r = 0; r < nd_; ++r) {
+                    if (r == q) continue;
+                    const int j = (q - r + nd_) % nd_;  // q is peer j of rank r
+                    if ((e = cudaStreamWaitEvent(S_[q].add, S_[r].scattered[static_cast<size_t>(k) * (nd_ - 1) + (j - 1)], 0)) != cudaSuccess) return e;
+                }
                 uint64_t off, len;
                 chunk_range(slice_len(q), k, &off, &len);
                 if (len) {
@@ -132,36 +253,57 @@ public:
                     if ((e = cudaGetLastError()) != cudaSuccess) return e;
                 }
                 if ((e = cudaEventRecord(S_[q].added[k], S_[q].add)) != cudaSuccess) return e;
-                if ((e = cudaStreamWaitEvent(S_[q].gather, S_[q].added[k], 0)) != cudaSuccess) return e;
-                for (int j = 1; j < nd_ && len; ++j) {
+                for (int j = 1; j < nd_; ++j) {
                     const int p = (q + j) % nd_;
-                    e = cudaMemcpyPeerAsync(R_[p].buf + slice_lo(q) + off, R_[p].ord, R_[q].buf + slice_lo(q) + off, R_[q].ord,
-                                            len * sizeof(uint32_t), S_[q].gather);
+                    if ((e = cudaStreamWaitEvent(S_[q].gather[j - 1], S_[q].added[k], 0)) != cudaSuccess) return e;
+                    if (!len) continue;
+                    e = cudaMemcpyAsync(R_[p].buf + slice_lo(q) + off, R_[q].buf + slice_lo(q) + off, len * sizeof(uint32_t),
+                                        cudaMemcpyDeviceToDevice, S_[q].gather[j - 1]);
                     if (e != cudaSuccess) return e;
                 }
             }
         for (int r = 0; r < nd_; ++r) {
             if ((e = cudaSetDevice(R_[r].ord)) != cudaSuccess) return e;
-            if ((e = cudaEventRecord(S_[r].gathered, S_[r].gather)) != cudaSuccess) return e;
+            for (int j = 1; j < nd_; ++j)
+                if ((e = cudaEventRecord(S_[r].gathered[j - 1], S_[r].gather[j - 1])) != cudaSuccess) return e;
         }
-        for (int r = 0; r < nd_; ++r) {
+        for (int r = 0; r < nd_; ++r) {  // a rank's round is over when its outgoing gathers have left and the incoming ones have landed
             if ((e = cudaSetDevice(R_[r].ord)) != cudaSuccess) return e;
-            for (int x = 0; x < nd_; ++x)
-                if ((e = cudaStreamWaitEvent(R_[r].main, S_[x].gathered, 0)) != cudaSuccess) return e;
+            for (int j = 1; j < nd_; ++j) {
+                const int q = (r - j + nd_) % nd_;  // r is peer j of rank q
+                if ((e = cudaStreamWaitEvent(mains[r], S_[r].gathered[j - 1], 0)) != cudaSuccess) return e;
+                if ((e = cudaStreamWaitEvent(mains[r], S_[q].gathered[j - 1], 0)) != cudaSuccess) return e;
+            }
         }
         return cudaSuccess;
     }
 
+public:
     // The caller has synchronised the devices.
     void destroy() {
+        if (graph_exec_) cudaGraphExecDestroy(graph_exec_);
+        graph_exec_ = nullptr;
+        if (!R_.empty() && cudaSetDevice(R_[0].ord) == cudaSuccess) {
+            if (origin_) cudaStreamDestroy(origin_);
+            if (ext_done_) cudaEventDestroy(ext_done_);
+            if (fork_) cudaEventDestroy(fork_);
+        }
+        origin_ = nullptr;
+        ext_done_ = fork_ = nullptr;
         for (int r = 0; r < static_cast<int>(S_.size()); ++r) {
             if (cudaSetDevice(R_[r].ord) != cudaSuccess) continue;
             Side &s = S_[r];
-            if (s.scatter) cudaStreamDestroy(s.scatter);
-            if (s.gather) cudaStreamDestroy(s.gather);
+            for (cudaStream_t st : s.scatter)
+                if (st) cudaStreamDestroy(st);
+            for (cudaStream_t st : s.gather)
+                if (st) cudaStreamDestroy(st);
             if (s.add) cudaStreamDestroy(s.add);
             if (s.go) cudaEventDestroy(s.go);
-            if (s.gathered) cudaEventDestroy(s.gathered);
+            for (cudaEvent_t ev : s.gathered)
+                if (ev) cudaEventDestroy(ev);
+            if (s.gmain) cudaStreamDestroy(s.gmain);
+            if (s.ext_go) cudaEventDestroy(s.ext_go);
+            if (s.join) cudaEventDestroy(s.join);
             for (cudaEvent_t ev : s.scattered)
                 if (ev) cudaEventDestroy(ev);
             for (cudaEvent_t ev : s.added)
@@ -175,9 +317,14 @@ public:
 
 private:
     struct Side {
-        cudaStream_t scatter = nullptr, gather = nullptr, add = nullptr;
-        cudaEvent_t go = nullptr, gathered = nullptr;
-        std::vector<cudaEvent_t> scattered, added;  // per chunk
+        std::vector<cudaStream_t> scatter, gather;  // one per peer: [j-1] serves rank (r + j) % n
+        cudaStream_t add = nullptr;
+        cudaStream_t gmain = nullptr;                  // this rank's main stream inside the captured graph
+        cudaEvent_t ext_go = nullptr, join = nullptr;  // caller's main -> origin; gmain -> origin
+        cudaEvent_t go = nullptr;
+        std::vector<cudaEvent_t> scattered;  // [chunk * (n-1) + j-1]
+        std::vector<cudaEvent_t> added;      // per chunk
+        std::vector<cudaEvent_t> gathered;   // per peer: the last gather to that peer
     };
     uint64_t slice_lo(int q) const { return std::min<uint64_t>(per_ * static_cast<uint64_t>(q), count_); }
     uint64_t slice_len(int q) const { return std::min<uint64_t>(slice_lo(q) + per_, count_) - slice_lo(q); }
@@ -188,6 +335,11 @@ private:
     }
     std::vector<CeRank> R_;
     std::vector<Side> S_;
+    bool graph_tried_ = false;
+    std::string graph_note_ = "graph not requested";
+    cudaGraphExec_t graph_exec_ = nullptr;
+    cudaStream_t origin_ = nullptr;
+    cudaEvent_t ext_done_ = nullptr, fork_ = nullptr;
     int nd_ = 0, chunks_ = 2;
     uint64_t count_ = 0, per_ = 0, chunk_words_ = 0;
 };

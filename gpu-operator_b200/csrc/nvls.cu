@@ -865,10 +865,21 @@ extern "C" int gpuprobe_allreduce_i32_auto(const gpuprobe_ar_cfg *cfg, gpuprobe_
         return GPUPROBE_EINVAL;
     }
     const int nd = cfg->ndev;
-    if (nd != 2 && nd != 4 && nd != 8) return allreduce_symmetric(cfg, out, 0, err, errlen);  // any rank count: NVLS only
-    int algo = nd == 2 ? 3 : 2;  // 2 ranks: all-push two-shot (646 vs 626 GB/s for pull+push); 4 and 8: hybrid (684 / 815)
-    if (const char *e = getenv("GPUPROBE_AR_AUTO_ALGO")) algo = std::max(0, std::min(3, atoi(e)));
+    const uint64_t bytes = cfg->count * sizeof(uint32_t);
+    // Measured (profiles/r02_fabric.md): large buffers at 2 and 4 ranks are fastest with the copy engines moving the data
+    // (748 / 717 GB/s busbw at 1 GiB against 646 / 684 for the best kernel); below the crossover the engines' start-up
+    // latency loses to one cooperative kernel. Odd rank counts: copy engines (any count) when large, NVLS otherwise.
+    int algo = nd == 2 ? 3 : 2;  // 2 ranks: all-push two-shot; 4 and 8: hybrid (815 GB/s at 8)
+    if (nd != 2 && nd != 4 && nd != 8) algo = 0;
+    const bool engines = (nd == 2 && bytes >= (32ull << 20)) || (nd > 2 && nd != 8 && bytes >= (512ull << 20));
+    if (const char *e = getenv("GPUPROBE_AR_AUTO_ALGO")) {
+        algo = std::max(0, std::min(5, atoi(e)));
+        if (algo == 5) return gpuprobe_allreduce_i32_ce(cfg, out, err, errlen);
+    } else if (engines) {
+        return gpuprobe_allreduce_i32_ce(cfg, out, err, errlen);
+    }
     int rc = allreduce_symmetric(cfg, out, algo, err, errlen);
-    if (rc == GPUPROBE_ENOPEER && algo != 1) rc = allreduce_symmetric(cfg, out, 1, err, errlen);  // no multicast on this box
+    if (rc == GPUPROBE_ENOPEER && algo != 1)  // no multicast on this box: peer mappings (2, 4, 8 ranks) or the copy engines
+        rc = (nd == 2 || nd == 4 || nd == 8) ? allreduce_symmetric(cfg, out, 1, err, errlen) : gpuprobe_allreduce_i32_ce(cfg, out, err, errlen);
     return rc;
 }

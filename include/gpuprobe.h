@@ -331,9 +331,11 @@ GPUPROBE_API int gpuprobe_allreduce_i32_ce(const gpuprobe_ar_cfg *cfg, gpuprobe_
  * No reference counterpart. */
 GPUPROBE_API int gpuprobe_allreduce_i32_nvls_ce(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
 
-/* The hand-written kernel the validator uses when GPUPROBE_AR_IMPL does not name one: the measured best for the
- * rank count (all-push two-shot at 2 ranks, hybrid at 4 and 8; profiles/r02_fabric.md), falling back to the
- * pull+push two-shot kernel when NVLink multicast is unavailable.  out->impl says which ran.  No reference counterpart. */
+/* What the validator runs when GPUPROBE_AR_IMPL does not name an implementation: the measured best for the rank count
+ * and size (profiles/r02_fabric.md) -- the copy-engine two-shot for large buffers at 2 ranks (>= 32 MiB) and at 3-7 ranks
+ * (>= 512 MiB), otherwise the all-push kernel at 2 ranks, the hybrid kernel at 4 and 8, NVLS at other counts; the
+ * peer-mapping two-shot or the copy engines where NVLink multicast is unavailable.  out->impl says which ran.
+ * No reference counterpart. */
 GPUPROBE_API int gpuprobe_allreduce_i32_auto(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
 
 /* Releases cached per-device state: streams, the digest/verify scratch, the staging slots and pinned

@@ -176,9 +176,16 @@ def test_p2p_copy_engine_modes_land_the_oracles_words(gp, ndev, mode):
 
 def test_auto_allreduce_picks_a_kernel_and_matches_oracle(gp, ndev):
     for nd in [n for n in (2, 4, 8) if n <= ndev]:
-        res = gp.allreduce_i32_auto(nd, (8 << 20) + 9, iters=2, warmup=1, seed=11)
+        res = gp.allreduce_i32_auto(nd, (8 << 20) + 9, iters=2, warmup=1, seed=11)  # 32 MiB: engines at 2 ranks only
         assert_reduced_buffer_matches_oracle(res, nd, (8 << 20) + 9, 11, 1, 2)
+        assert res.impl == (gp.AR_IMPL_CE if nd == 2 else gp.AR_IMPL_HYBRID)
+        res = gp.allreduce_i32_auto(nd, (1 << 20) + 9, iters=2, warmup=1, seed=11)  # 4 MiB: one cooperative kernel
+        assert_reduced_buffer_matches_oracle(res, nd, (1 << 20) + 9, 11, 1, 2)
         assert res.impl == (gp.AR_IMPL_PUSH if nd == 2 else gp.AR_IMPL_HYBRID)
+    if ndev >= 4:
+        res = gp.allreduce_i32_auto(4, 1 << 27, iters=2, warmup=1, seed=11)  # 512 MiB at 4 ranks: engines
+        assert_reduced_buffer_matches_oracle(res, 4, 1 << 27, 11, 1, 2)
+        assert res.impl == gp.AR_IMPL_CE
 
 
 def test_two_shot_allreduce_without_multicast(gp, ndev, monkeypatch):
