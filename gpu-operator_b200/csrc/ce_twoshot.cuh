@@ -71,7 +71,20 @@ public:
         chunks_ = chunks > 0 ? chunks : 2;
         if (const char *e = getenv("GPUPROBE_CE_CHUNKS")) chunks_ = std::max(1, std::min(64, atoi(e)));
         while (chunks_ > 1 && per_ / chunks_ < (1u << 18)) chunks_ /= 2;
-        chunk_words_ = ((per_ + chunks_ - 1) / chunks_ + 31) & ~31ull;
+        // Chunk boundaries inside a slice: equal chunks. GPUPROBE_CE_FIRST_PERMILLE gives the first chunk another share
+        // (a bigger first chunk would hide the last add; measured, it loses: 2 ranks 740 / 742 / 713 / 676 / 654 GB/s for
+        // 50 / 65 / 75 / 85 / 92 % -- profiles/r02_fabric.md).
+        int first_permille = 1000 / chunks_;
+        if (const char *e = getenv("GPUPROBE_CE_FIRST_PERMILLE")) first_permille = std::max(1, std::min(999, atoi(e)));
+        bounds_.assign(chunks_ + 1, per_);
+        bounds_[0] = 0;
+        if (chunks_ > 1) {
+            bounds_[1] = getenv("GPUPROBE_CE_FIRST_PERMILLE") ? std::min<uint64_t>(per_, (per_ / 1000u * static_cast<uint64_t>(first_permille) + 31) & ~31ull)
+                                                              : std::min<uint64_t>(per_, ((per_ + chunks_ - 1) / chunks_ + 31) & ~31ull);
+            const uint64_t rest = per_ - bounds_[1];
+            for (int k = 2; k < chunks_; ++k)
+                bounds_[k] = std::min<uint64_t>(per_, bounds_[1] + ((rest / (chunks_ - 1) * static_cast<uint64_t>(k - 1) + 31) & ~31ull));
+        }
         S_.resize(nd_);
         cudaError_t e;
         for (int r = 0; r < nd_; ++r) {
@@ -330,8 +343,8 @@ private:
     uint64_t slice_len(int q) const { return std::min<uint64_t>(slice_lo(q) + per_, count_) - slice_lo(q); }
     // words [off, off+len) of chunk k inside a slice of `len_slice` words
     void chunk_range(uint64_t len_slice, int k, uint64_t *off, uint64_t *len) const {
-        *off = std::min<uint64_t>(chunk_words_ * static_cast<uint64_t>(k), len_slice);
-        *len = std::min<uint64_t>(*off + chunk_words_, len_slice) - *off;
+        *off = std::min<uint64_t>(bounds_[k], len_slice);
+        *len = std::min<uint64_t>(bounds_[k + 1], len_slice) - *off;
     }
     std::vector<CeRank> R_;
     std::vector<Side> S_;
@@ -341,7 +354,8 @@ private:
     cudaStream_t origin_ = nullptr;
     cudaEvent_t ext_done_ = nullptr, fork_ = nullptr;
     int nd_ = 0, chunks_ = 2;
-    uint64_t count_ = 0, per_ = 0, chunk_words_ = 0;
+    uint64_t count_ = 0, per_ = 0;
+    std::vector<uint64_t> bounds_;  // chunk k of a slice = words [bounds_[k], bounds_[k+1]) of it (multiples of 32)
 };
 
 }  // namespace gp

@@ -868,10 +868,11 @@ extern "C" int gpuprobe_allreduce_i32_auto(const gpuprobe_ar_cfg *cfg, gpuprobe_
     const uint64_t bytes = cfg->count * sizeof(uint32_t);
     // Measured (profiles/r02_fabric.md): large buffers at 2 and 4 ranks are fastest with the copy engines moving the data
     // (748 / 717 GB/s busbw at 1 GiB against 646 / 684 for the best kernel); below the crossover the engines' start-up
-    // latency loses to one cooperative kernel. Odd rank counts: copy engines (any count) when large, NVLS otherwise.
+    // latency loses to one cooperative kernel; from 5 ranks up the engines' many concurrent copies lose to the switch
+    // (8 ranks: 426 against 816). Other rank counts than 2, 4, 8: NVLS, or the engines at 3 ranks.
     int algo = nd == 2 ? 3 : 2;  // 2 ranks: all-push two-shot; 4 and 8: hybrid (815 GB/s at 8)
     if (nd != 2 && nd != 4 && nd != 8) algo = 0;
-    const bool engines = (nd == 2 && bytes >= (32ull << 20)) || (nd > 2 && nd != 8 && bytes >= (512ull << 20));
+    const bool engines = (nd == 2 && bytes >= (32ull << 20)) || ((nd == 3 || nd == 4) && bytes >= (512ull << 20));
     if (const char *e = getenv("GPUPROBE_AR_AUTO_ALGO")) {
         algo = std::max(0, std::min(5, atoi(e)));
         if (algo == 5) return gpuprobe_allreduce_i32_ce(cfg, out, err, errlen);

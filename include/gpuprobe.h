@@ -332,7 +332,7 @@ GPUPROBE_API int gpuprobe_allreduce_i32_ce(const gpuprobe_ar_cfg *cfg, gpuprobe_
 GPUPROBE_API int gpuprobe_allreduce_i32_nvls_ce(const gpuprobe_ar_cfg *cfg, gpuprobe_ar_result *out, char *err, size_t errlen);
 
 /* What the validator runs when GPUPROBE_AR_IMPL does not name an implementation: the measured best for the rank count
- * and size (profiles/r02_fabric.md) -- the copy-engine two-shot for large buffers at 2 ranks (>= 32 MiB) and at 3-7 ranks
+ * and size (profiles/r02_fabric.md) -- the copy-engine two-shot for large buffers at 2 ranks (>= 32 MiB) and at 3-4 ranks
  * (>= 512 MiB), otherwise the all-push kernel at 2 ranks, the hybrid kernel at 4 and 8, NVLS at other counts; the
  * peer-mapping two-shot or the copy engines where NVLink multicast is unavailable.  out->impl says which ran.
  * No reference counterpart. */

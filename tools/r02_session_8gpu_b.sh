@@ -4,7 +4,7 @@ set -u
 O=gpurun_out
 mkdir -p $O
 export GPUPROBE_NCCL_LIB=$(python -c "import importlib.util,os;s=importlib.util.find_spec('nvidia.nccl');print(os.path.join(list(s.submodule_search_locations)[0],'lib','libnccl.so.2'))")
-for k in 1 2 4; do GPUPROBE_CE_CHUNKS=$k timeout 300 python tools/nvls_probe.py --ndevs 4,8 --counts 28 --impls copy_engine --tag chunks$k >> $O/r02_ar_ce_8gpu.jsonl 2>> $O/r02_ar_ce_8gpu.err; done
+for k in 1 2 3 4; do GPUPROBE_CE_CHUNKS=$k timeout 300 python tools/nvls_probe.py --ndevs 8,4 --counts 28 --impls copy_engine --tag chunks$k >> $O/r02_ar_ce_8gpu.jsonl 2>> $O/r02_ar_ce_8gpu.err; done
 for p in 500 650 800 900; do GPUPROBE_NVLSCE_PERMILLE=$p timeout 300 python tools/nvls_probe.py --ndevs 8,4 --counts 28 --impls nvls_ce --tag permille$p >> $O/r02_ar_ce_8gpu.jsonl 2>> $O/r02_ar_ce_8gpu.err; done
 GPUPROBE_NVLS_CTAS=2 GPUPROBE_NVLSCE_PERMILLE=800 timeout 300 python tools/nvls_probe.py --ndevs 8 --counts 28 --impls nvls_ce --tag permille800_ctas2 >> $O/r02_ar_ce_8gpu.jsonl 2>> $O/r02_ar_ce_8gpu.err
 timeout 300 python tools/nvls_probe.py --ndevs 8 --counts 28 --impls hybrid,nvls --tag same_box >> $O/r02_ar_ce_8gpu.jsonl 2>> $O/r02_ar_ce_8gpu.err
