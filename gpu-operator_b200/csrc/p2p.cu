@@ -539,3 +539,103 @@ extern "C" int gpuprobe_p2p_matrix(const gpuprobe_p2p_cfg *cfg, gpuprobe_p2p_cel
     return GPUPROBE_OK;
 #undef GP_TRY
 }
+
+// The P2P kernels with source and landing buffer on ONE device: no link is crossed, so this says nothing about NVLink --
+// it exists so that the same kernels and their checksum reduction can be checked against the oracle on a box with a
+// single GPU (the plugin workload's pod, a 1-GPU test machine). cell->gbps is then local HBM copy bandwidth.
+extern "C" int gpuprobe_p2p_loopback(int dev, uint64_t bytes, int iters, int kernel, uint32_t seed, gpuprobe_p2p_cell *cell,
+                                     char *err, size_t errlen) {
+    if (!cell || bytes == 0 || (bytes & 15u) || iters < 1 || kernel < 0 || kernel > 1) {
+        set_err(err, errlen, "bad p2p loopback arguments: bytes=%llu iters=%d kernel=%d", (unsigned long long)bytes, iters, kernel);
+        return GPUPROBE_EINVAL;
+    }
+    std::memset(cell, 0, sizeof(*cell));
+    DeviceState *st = nullptr;
+    int rc = use_device(dev, &st, err, errlen);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lock(st->mu);
+    const uint64_t nwords = bytes / 4, n16 = bytes / 16;
+    uint32_t *src = nullptr, *dst = nullptr;
+    P2PScratch *scr = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    auto cleanup = [&]() {
+        cudaDeviceSynchronize();
+        cudaFree(src);
+        cudaFree(dst);
+        cudaFree(scr);
+        if (ev0) cudaEventDestroy(ev0);
+        if (ev1) cudaEventDestroy(ev1);
+        (void)cudaGetLastError();
+    };
+#define GP_TRY(call)                                                                                   \
+    do {                                                                                               \
+        cudaError_t e_ = (call);                                                                       \
+        if (e_ != cudaSuccess) {                                                                       \
+            set_err(err, errlen, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            (void)cudaGetLastError();                                                                  \
+            cleanup();                                                                                 \
+            return e_ == cudaErrorMemoryAllocation ? GPUPROBE_ENOMEM : GPUPROBE_ECUDA;                 \
+        }                                                                                              \
+    } while (0)
+    GP_TRY(cudaMalloc(&src, bytes));
+    GP_TRY(cudaMalloc(&dst, bytes));
+    GP_TRY(cudaMalloc(&scr, sizeof(P2PScratch)));
+    GP_TRY(cudaMemsetAsync(scr, 0, sizeof(P2PScratch), st->stream));
+    GP_TRY(cudaMemsetAsync(dst, 0, bytes, st->stream));
+    GP_TRY(cudaEventCreate(&ev0));
+    GP_TRY(cudaEventCreate(&ev1));
+    rc = launch_fill_words(*st, src, nwords, hash_base(seed, stream_p2p(dev)), st->stream, err, errlen);
+    if (rc) {
+        cleanup();
+        return rc;
+    }
+    if (kernel == 0)
+        GP_TRY(cudaFuncSetAttribute(p2p_bulk_copy_checksum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(P2PB_SMEM)));
+    std::vector<float> ms(iters);
+    for (int i = 0; i < iters + 1; ++i) {  // one untimed launch first
+        if (i) GP_TRY(cudaEventRecord(ev0, st->stream));
+        if (kernel == 0)
+            p2p_bulk_copy_checksum_kernel<<<p2p_bulk_grid(*st, bytes), P2PB_THREADS, P2PB_SMEM, st->stream>>>(
+                reinterpret_cast<const unsigned char *>(src), reinterpret_cast<unsigned char *>(dst), bytes, scr);
+        else
+            p2p_copy_checksum_kernel<<<p2p_grid(*st, n16), P2P_THREADS, 0, st->stream>>>(reinterpret_cast<const uint4 *>(src),
+                                                                                         reinterpret_cast<uint4 *>(dst), n16, scr);
+        GP_TRY(cudaGetLastError());
+        if (i) {
+            GP_TRY(cudaEventRecord(ev1, st->stream));
+            GP_TRY(cudaEventSynchronize(ev1));
+            GP_TRY(cudaEventElapsedTime(&ms[i - 1], ev0, ev1));
+        }
+    }
+    P2PScratch head{};
+    GP_TRY(cudaMemcpyAsync(&head, scr, 16, cudaMemcpyDeviceToHost, st->stream));
+    GP_TRY(cudaStreamSynchronize(st->stream));
+    uint64_t land_sum = 0;
+    uint32_t land_xor = 0;
+    rc = run_digest(*st, dst, nwords, &land_sum, &land_xor, st->stream, err, errlen);
+    if (rc) {
+        cleanup();
+        return rc;
+    }
+    cell->src = cell->dst = dev;
+    cell->peer_ok = 1;
+    gpuprobe_p2p_expected(nwords, seed, dev, 0, &cell->checksum_expected, &cell->xor_expected);
+    cell->checksum_got = head.out_sum;
+    cell->xor_got = head.out_xor;
+    cell->verified = (head.out_sum == cell->checksum_expected && head.out_xor == cell->xor_expected && land_sum == cell->checksum_expected &&
+                      land_xor == cell->xor_expected)
+                         ? 1
+                         : 0;
+    cell->ms_best = *std::min_element(ms.begin(), ms.end());
+    cell->ms_median = median_of(ms);
+    cell->gbps = cell->ms_median > 0 ? bytes / (cell->ms_median * 1e6) : 0;
+    cell->frac_of_peak = 0;  // no link involved
+    cleanup();
+    if (!cell->verified) {
+        set_err(err, errlen, "p2p loopback on device %d: checksum %016llx, expected %016llx", dev, (unsigned long long)cell->checksum_got,
+                (unsigned long long)cell->checksum_expected);
+        return GPUPROBE_FAIL_VERIFY;
+    }
+    return GPUPROBE_OK;
+#undef GP_TRY
+}

@@ -125,6 +125,7 @@ SIGNATURES = {
     "gpuprobe_host_alloc": (_int, [C.POINTER(C.c_void_p), C.c_size_t]),
     "gpuprobe_host_free": (_int, [C.c_void_p]),
     "gpuprobe_p2p_matrix": (_int, [C.POINTER(P2PCfg), C.POINTER(P2PCell), *_err]),
+    "gpuprobe_p2p_loopback": (_int, [_int, _u64, _int, _int, _u32, C.POINTER(P2PCell), *_err]),
     "gpuprobe_p2p_expected": (None, [_u64, _u32, _int, _int, C.POINTER(_u64), C.POINTER(_u32)]),
     "gpuprobe_allreduce_i32": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
     "gpuprobe_allreduce_i32_nvls": (_int, [C.POINTER(ArCfg), C.POINTER(ArResult), *_err]),
@@ -290,6 +291,13 @@ def p2p_expected(nwords: int, seed: int, src: int, threads: int = 0):
     s, x = _u64(0), _u32(0)
     lib.gpuprobe_p2p_expected(nwords, seed, src, threads, C.byref(s), C.byref(x))
     return s.value, x.value
+
+
+def p2p_loopback(nbytes: int, dev: int = 0, iters: int = 3, kernel: int = 0, seed: int = 0) -> P2PCell:
+    """gpuprobe_p2p_loopback: the P2P copy+checksum kernels with both buffers on one device (kernel 0 = bulk ring, 1 = ldst)."""
+    cell, eb = P2PCell(), _errbuf()
+    _check(lib.gpuprobe_p2p_loopback(dev, nbytes, iters, kernel, seed, C.byref(cell), eb, len(eb)), "gpuprobe_p2p_loopback", eb)
+    return cell
 
 
 def p2p_matrix(ndev: int, bytes_per_pair: int, iters: int = 10, warmup: int = 3, mode: int = P2P_SERIAL,

@@ -192,6 +192,19 @@ int main(void) {
                  << "# TYPE gpu_operator_node_cuda_p2p_min_gbps gauge\n"
                  << "gpu_operator_node_cuda_p2p_min_gbps{node=\"@NODE@\"} " << mn << "\n";
     }
+    if (p2pBytes && ndev == 1) {
+        // one visible GPU (the plugin workload's pod): no link to probe, but the copy+checksum kernel itself can still be
+        // checked, looped back on the device
+        gpuprobe_p2p_cell cell{};
+        rc = gpuprobe_p2p_loopback(0, p2pBytes & ~15ull, 3, 0, 0, &cell, err, sizeof(err));
+        if (rc != GPUPROBE_OK) {
+            ++failed;
+            fprintf(stderr, "P2P kernel loopback failed: %s %s\n", gpuprobe_strerror(rc), err);
+        }
+        printf("P2P kernel loopback on the one visible GPU: %.1f GB/s local copy, checksum %s\n", cell.gbps, cell.verified ? "ok" : "BAD");
+        json << ",\"p2p_loopback\":{\"rc\":" << rc << ",\"bytes\":" << (p2pBytes & ~15ull) << ",\"gbps\":" << cell.gbps
+             << ",\"verified\":" << (cell.verified ? "true" : "false") << "}";
+    }
     const unsigned long long arCount = envU64("GPUPROBE_AR_COUNT");
     if (arCount && ndev >= 2) {
         gpuprobe_ar_cfg cfg{};

@@ -278,6 +278,13 @@ GPUPROBE_API int gpuprobe_host_free(void *p);
  * no peer access (its cell has peer_ok = 0). */
 GPUPROBE_API int gpuprobe_p2p_matrix(const gpuprobe_p2p_cfg *cfg, gpuprobe_p2p_cell *cells, char *err, size_t errlen);
 
+/* The same two kernels (kernel: 0 = cp.async.bulk ring, 1 = register path) with source and landing buffer on ONE device.
+ * No link is crossed, so this is not a fabric figure (cell->gbps is local HBM copy bandwidth, frac_of_peak stays 0); it
+ * lets the kernels and their checksum reduction be checked against the expected value where only one GPU is visible --
+ * the plugin workload's pod (validator/main.go:973-983 allocates it one GPU) or a single-GPU test box.  New capability. */
+GPUPROBE_API int gpuprobe_p2p_loopback(int dev, uint64_t bytes, int iters, int kernel, uint32_t seed, gpuprobe_p2p_cell *cell,
+                                       char *err, size_t errlen);
+
 /* Expected checksum of source `src`'s buffer, computed on the host (threads <= 0: all). */
 GPUPROBE_API void gpuprobe_p2p_expected(uint64_t nwords, uint32_t seed, int src, int threads, uint64_t *sum64,
                            uint32_t *xor32);

@@ -382,3 +382,19 @@ def test_digest_and_verify_share_cached_scratch_across_threads_and_streams(gp, t
     for t in threads:
         t.join()
     assert not errors, errors
+
+
+@pytest.mark.parametrize("kernel", [0, 1])
+def test_p2p_kernels_loop_back_on_one_gpu_against_oracle(gp, kernel):
+    """gpuprobe_p2p_loopback: the P2P copy+checksum kernels (0 = cp.async.bulk ring, 1 = register path) with both buffers
+    on one device, so that their checksum reduction and the landed copy are checked against the oracle where only one GPU
+    is visible. Sizes: below one 32 KiB chunk, ragged past several chunks, and large enough for every CTA to loop."""
+    for nbytes, seed in [(16, 1), (32768 - 16, 2), ((3 << 20) + 16 * 5, 3), (256 << 20, 4)]:
+        c = gp.p2p_loopback(nbytes, dev=0, iters=2, kernel=kernel, seed=seed)
+        want = oc.p2p_checksum(nbytes // 4, seed, 0)
+        assert c.verified == 1 and (c.src, c.dst) == (0, 0)
+        assert (c.checksum_got, c.xor_got) == want == (c.checksum_expected, c.xor_expected)
+    assert c.gbps > 500, f"{c.gbps:.0f} GB/s is not an HBM copy"
+    with pytest.raises(gp.GpuProbeError) as e:
+        gp.p2p_loopback(1000, kernel=kernel)  # not a multiple of 16
+    assert e.value.code == gp.EINVAL
