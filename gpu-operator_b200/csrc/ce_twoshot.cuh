@@ -85,6 +85,11 @@ public:
             for (int k = 2; k < chunks_; ++k)
                 bounds_[k] = std::min<uint64_t>(per_, bounds_[1] + ((rest / (chunks_ - 1) * static_cast<uint64_t>(k - 1) + 31) & ~31ull));
         }
+        // copy streams per rank and phase: one per peer up to 4 ranks (peer j uses stream (j-1) mod ns_), a single one
+        // beyond -- more concurrent copies than that are more than the DMA engines serve well (8 ranks, 1 GiB: 576 GB/s
+        // with 1 stream per phase, 469 with 2, 428 with 3, 424 with 7; profiles/r02_fabric.md).
+        ns_ = nd_ <= 4 ? nd_ - 1 : 1;
+        if (const char *e = getenv("GPUPROBE_CE_STREAMS")) ns_ = std::max(1, std::min(nd_ - 1, atoi(e)));
         S_.resize(nd_);
         cudaError_t e;
         for (int r = 0; r < nd_; ++r) {
@@ -94,8 +99,8 @@ public:
             if ((e = cudaDeviceGetStreamPriorityRange(&lo, &hi)) != cudaSuccess) return e;
             // one copy stream per peer and phase: the n-1 transfers of a chunk run side by side, so the start-up gap
             // of one copy is covered by the others (serial copies on one stream lose ~15 us per copy)
-            s.scatter.assign(nd_ - 1, nullptr);
-            s.gather.assign(nd_ - 1, nullptr);
+            s.scatter.assign(ns_, nullptr);
+            s.gather.assign(ns_, nullptr);
             for (auto &st : s.scatter)
                 if ((e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking)) != cudaSuccess) return e;
             for (auto &st : s.gather)
@@ -243,10 +248,10 @@ private:
                         const int slot = r < q ? r : r - 1;
                         // unified addressing tells the driver which two devices these are; this form is also what stream capture takes
                         e = cudaMemcpyAsync(R_[q].stage + static_cast<uint64_t>(slot) * per_ + off, R_[r].buf + slice_lo(q) + off,
-                                            len * sizeof(uint32_t), cudaMemcpyDeviceToDevice, S_[r].scatter[j - 1]);
+                                            len * sizeof(uint32_t), cudaMemcpyDeviceToDevice, S_[r].scatter[(j - 1) % ns_]);
                         if (e != cudaSuccess) return e;
                     }
-                    if ((e = cudaEventRecord(S_[r].scattered[static_cast<size_t>(k) * (nd_ - 1) + (j - 1)], S_[r].scatter[j - 1])) != cudaSuccess) return e;
+                    if ((e = cudaEventRecord(S_[r].scattered[static_cast<size_t>(k) * (nd_ - 1) + (j - 1)], S_[r].scatter[(j - 1) % ns_])) != cudaSuccess) return e;
                 }
             }
         for (int k = 0; k < chunks_; ++k)  // add once every peer's copy of the chunk is here, then gather it to everyone
@@ -268,17 +273,17 @@ private:
                 if ((e = cudaEventRecord(S_[q].added[k], S_[q].add)) != cudaSuccess) return e;
                 for (int j = 1; j < nd_; ++j) {
                     const int p = (q + j) % nd_;
-                    if ((e = cudaStreamWaitEvent(S_[q].gather[j - 1], S_[q].added[k], 0)) != cudaSuccess) return e;
+                    if ((e = cudaStreamWaitEvent(S_[q].gather[(j - 1) % ns_], S_[q].added[k], 0)) != cudaSuccess) return e;
                     if (!len) continue;
                     e = cudaMemcpyAsync(R_[p].buf + slice_lo(q) + off, R_[q].buf + slice_lo(q) + off, len * sizeof(uint32_t),
-                                        cudaMemcpyDeviceToDevice, S_[q].gather[j - 1]);
+                                        cudaMemcpyDeviceToDevice, S_[q].gather[(j - 1) % ns_]);
                     if (e != cudaSuccess) return e;
                 }
             }
         for (int r = 0; r < nd_; ++r) {
             if ((e = cudaSetDevice(R_[r].ord)) != cudaSuccess) return e;
             for (int j = 1; j < nd_; ++j)
-                if ((e = cudaEventRecord(S_[r].gathered[j - 1], S_[r].gather[j - 1])) != cudaSuccess) return e;
+                if ((e = cudaEventRecord(S_[r].gathered[j - 1], S_[r].gather[(j - 1) % ns_])) != cudaSuccess) return e;
         }
         for (int r = 0; r < nd_; ++r) {  // a rank's round is over when its outgoing gathers have left and the incoming ones have landed
             if ((e = cudaSetDevice(R_[r].ord)) != cudaSuccess) return e;
@@ -330,7 +335,7 @@ public:
 
 private:
     struct Side {
-        std::vector<cudaStream_t> scatter, gather;  // one per peer: [j-1] serves rank (r + j) % n
+        std::vector<cudaStream_t> scatter, gather;  // ns_ each: stream (j-1) % ns_ serves rank (r + j) % n
         cudaStream_t add = nullptr;
         cudaStream_t gmain = nullptr;                  // this rank's main stream inside the captured graph
         cudaEvent_t ext_go = nullptr, join = nullptr;  // caller's main -> origin; gmain -> origin
@@ -353,7 +358,7 @@ private:
     cudaGraphExec_t graph_exec_ = nullptr;
     cudaStream_t origin_ = nullptr;
     cudaEvent_t ext_done_ = nullptr, fork_ = nullptr;
-    int nd_ = 0, chunks_ = 2;
+    int nd_ = 0, chunks_ = 2, ns_ = 1;
     uint64_t count_ = 0, per_ = 0;
     std::vector<uint64_t> bounds_;  // chunk k of a slice = words [bounds_[k], bounds_[k+1]) of it (multiples of 32)
 };
