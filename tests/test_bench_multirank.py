@@ -21,8 +21,9 @@ rank, world = dist.get_rank(), dist.get_world_size()
 ms_local = 10.0 + 5.0 * rank           # rank 1 is the slow one
 ms_max = bench.max_over_ranks(ms_local, "cpu")
 value = bench.whole_job_gbps(1 << 20, world, 7, ms_max / 1e3)
+every = bench.gather_over_ranks(ms_local, "cpu")   # per-rank times, in rank order, on every rank
 dist.barrier()
-print(json.dumps({"rank": rank, "world": world, "ms_max": ms_max, "value": value}), flush=True)
+print(json.dumps({"rank": rank, "world": world, "ms_max": ms_max, "value": value, "every": every}), flush=True)
 dist.destroy_process_group()
 '''
 
@@ -52,6 +53,7 @@ def test_max_over_ranks_and_whole_job_value_gloo_world2(tmp_path):
 
     # two ranks share one stdout: their lines can land on the same line, so pick the JSON objects out by shape
     rows = [json.loads(m) for m in re.findall(r"\{[^{}]*\}", r.stdout)]
+    assert all(x["every"] == [10.0, 15.0] for x in rows)  # what per_gpu_gbps at N > 1 is computed from
     assert sorted(x["rank"] for x in rows) == [0, 1]
     for x in rows:
         assert x["world"] == 2
@@ -65,6 +67,7 @@ def test_single_process_helpers_need_no_process_group():
     import bench
 
     assert bench.max_over_ranks(3.5) == 3.5
+    assert bench.gather_over_ranks(3.5) == [3.5]
     assert bench.whole_job_gbps(1 << 30, 1, 1, 1.0) == pytest.approx(12 * (1 << 30) / 1e9)
 
 
