@@ -15,6 +15,14 @@
 // staging copy. Per GPU roughly count*4*(1 + 1/n) bytes leave and the same arrive, against 2(n-1)/n * count*4 each
 // way for a ring, which is why busbw (= algbw * 2(n-1)/n) can exceed the 900 GB/s link figure.
 //
+// The same launch structure (one cooperative kernel per GPU, buffers mapped on every rank, flag barriers with a timeout)
+// carries the other kernels of this file, selected by `algo`:
+//     1  two-shot over peer mappings       pull-reduce my slice from every rank, push the sum to every rank
+//     2  hybrid                            head of the slice through the switch, tail over peer mappings, disjoint CTAs
+//     3  all-push two-shot                 scatter to the owner's staging area, add out of local HBM, broadcast: stores only
+//     4  NVLS + copy engines               this kernel on the head of the buffer, ce_twoshot.cuh on the tail (measured: no gain)
+// and gpuprobe_allreduce_i32_auto picks among them and the copy-engine two-shot by rank count and size.
+//
 // The reference has no counterpart.
 //
 // Driver-API calls (cuMem*, cuMulticast*) are resolved with cudaGetDriverEntryPoint, so the library still has
